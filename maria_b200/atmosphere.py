@@ -1,0 +1,455 @@
+"""``Atmosphere`` and ``AutoregressiveProcess`` with maria's interface (maria/atmosphere/atmosphere.py:31-380,
+maria/atmosphere/process.py:19-209), running on one B200 through libmaria_atm.so.
+
+Set-up geometry and the propagator matrices are float64 numpy / LAPACK on the host, once per plan (``host.py``).
+Layer generation (the AR recurrence), beam smoothing, line-of-sight sampling and everything downstream are CUDA.
+There is no CPU path: without the library or without a GPU these classes raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import time as ttime
+
+import numpy as np
+import scipy as sp
+import scipy.interpolate
+
+from . import _lib, host, inputs
+
+logger = logging.getLogger("maria_b200")
+
+SUPPORTED_MODELS_LIST = ["2d", "3d"]
+_PRECISIONS = {"fp32": _lib.F32, "float32": _lib.F32, "fp64": _lib.F64, "float64": _lib.F64}
+
+
+def _torch():
+    import torch
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("maria_b200 needs a CUDA device (there is no CPU fallback)")
+    return torch
+
+
+class DeviceContext:
+    """One libmaria_atm handle (= one GPU, one arithmetic type) plus the status -> exception mapping of
+    SURVEY.md section 8b."""
+
+    def __init__(self, device=0, precision="fp32"):
+        if precision not in _PRECISIONS:
+            raise ValueError(f"Invalid precision '{precision}'. Supported: fp32, fp64.")
+        self.torch = _torch()
+        self.lib = _lib.load()
+        self.device = int(device)
+        self.precision = "fp64" if _PRECISIONS[precision] == _lib.F64 else "fp32"
+        self.dtype_code = _PRECISIONS[precision]
+        self.torch_dtype = self.torch.float64 if self.dtype_code == _lib.F64 else self.torch.float32
+        self.np_dtype = np.float64 if self.dtype_code == _lib.F64 else np.float32
+        h = C.c_void_p()
+        rc = self.lib.matm_create(self.device, self.dtype_code, C.byref(h))
+        if rc != _lib.OK:
+            raise RuntimeError(f"matm_create failed on cuda:{device} (status {rc})")
+        self.h = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                self.lib.matm_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc == _lib.OK:
+            return
+        buf = C.create_string_buffer(1024)
+        self.lib.matm_last_error(self.h, buf, 1024)
+        msg = buf.value.decode(errors="replace")
+        if rc == _lib.ERR_ARG:
+            raise RuntimeError(msg)
+        raise RuntimeError(f"libmaria_atm status {rc}: {msg}")
+
+    def stream_ptr(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def empty(self, shape, dtype=None):
+        return self.torch.empty(shape, dtype=dtype or self.torch_dtype, device=f"cuda:{self.device}")
+
+    def to_device(self, a, dtype):
+        return self.torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(f"cuda:{self.device}")
+
+    def raise_on_flags(self):
+        st, layer, det, sample = C.c_int(), C.c_int(), C.c_int64(), C.c_int64()
+        self.check(self.lib.matm_check_flags(self.h, C.byref(st), C.byref(layer), C.byref(det), C.byref(sample)))
+        return st.value, layer.value, det.value, sample.value
+
+    @property
+    def launch_count(self):
+        return int(self.lib.matm_launch_count(self.h))
+
+
+class AutoregressiveProcess:
+    """Sparse-precision autoregressive Gaussian process of arXiv:2111.01319 (maria/atmosphere/process.py:19-209).
+    ``cross_section`` is (n_cs, 2) = (x, height), ``extrusion`` is (n_ext,)."""
+
+    def __init__(self, cross_section, extrusion, callback=None, callback_kwargs=None, jitter=1e-6,
+                 MIN_SAMPLES_PER_LAYER=4):
+        self.cross_section = np.asarray(cross_section, dtype=float)
+        self.extrusion = np.asarray(extrusion, dtype=float)
+        self.callback_kwargs = dict(callback_kwargs or {})
+        self.callback = callback if callback is not None else host.MaternTable(**self.callback_kwargs)
+        self.jitter = jitter
+        self.n_cross_section, self.n_extrusion = len(self.cross_section), len(self.extrusion)
+        self.extrusion_sample_index, self.cross_section_sample_index = host.build_stencil(
+            self.n_extrusion, self.n_cross_section, MIN_SAMPLES_PER_LAYER)
+        self.sample_points = np.c_[self.extrusion[self.extrusion_sample_index],
+                                   self.cross_section[self.cross_section_sample_index]]  # process.py:72-89
+        self.n_sample = len(self.sample_points)
+        self.live_edge_points = np.c_[
+            self.extrusion[0] * np.ones(self.n_cross_section) - np.gradient(self.extrusion).mean(),
+            self.cross_section]  # process.py:91-100
+        self.n_live_edge = self.n_cross_section
+        if self.n_sample > 4000:  # process.py:102-107
+            logger.warning(f"n_sample = {self.n_sample}: inverting the sample covariance is very expensive")
+        self._dev = None
+        self._values_host = None
+
+    def compute_covariance_matrices(self, rng=np.random):
+        """process.py:111-189.  Draws (and discards, as the reference effectively does) the initial slice so that the
+        host random stream stays aligned with the reference."""
+        t0 = ttime.monotonic()
+        self.A, self.B, C_EE = host.propagator_matrices(self.sample_points, self.live_edge_points, self.callback, self.jitter)
+        rng.standard_normal(self.n_cross_section)  # process.py:182, overwritten by run()
+        logger.debug(f"Computed covariance matrices ({self.n_cross_section} x {self.n_sample}) in "
+                     f"{ttime.monotonic() - t0:.3f} s")
+
+    # ---- device side ----
+    def bind(self, ctx):
+        """Upload A, B and the stencil; allocate BUFFER (3 n_ext, n_cs) and Z (2 n_ext, n_cs) on the device."""
+        tc = ctx.torch
+        self._ctx = ctx
+        self._dev = dict(
+            A=ctx.to_device(self.A, tc.float64), B=ctx.to_device(self.B, tc.float64),
+            esi=ctx.to_device(self.extrusion_sample_index.astype(np.int32), tc.int32),
+            csi=ctx.to_device(self.cross_section_sample_index.astype(np.int32), tc.int32),
+            buffer=ctx.empty((3 * self.n_extrusion, self.n_cross_section), tc.float64),
+            z=ctx.empty((2 * self.n_extrusion, self.n_cross_section), tc.float64),
+        )
+
+    def run(self, rng=None, seed=None, subsequence=0):
+        """process.py:191-209.  ``rng`` (host, e.g. ``np.random``): validation mode, the noise is drawn on the host in
+        the reference's order and uploaded.  ``seed``: production mode, Philox noise on the device."""
+        if self._dev is None:
+            raise RuntimeError("AutoregressiveProcess must be bound to a device context before run().")
+        ctx, dv = self._ctx, self._dev
+        n_ext, n_cs = self.n_extrusion, self.n_cross_section
+        st = ctx.stream_ptr()
+        tail = dv["buffer"][2 * n_ext:]
+        if rng is not None:
+            buffer0 = rng.standard_normal((3 * n_ext, n_cs))  # process.py:196-198 (only the last n_ext rows are read)
+            z = rng.standard_normal((2 * n_ext, n_cs))        # process.py:206, one row per executed step
+            tail.copy_(ctx.torch.from_numpy(buffer0[2 * n_ext:]))
+            dv["z"].copy_(ctx.torch.from_numpy(z))
+        else:
+            if seed is None:
+                raise ValueError("either a host rng or a Philox seed is required")
+            ctx.check(ctx.lib.matm_fill_normal(ctx.h, tail.data_ptr(), tail.numel(), seed, 2 * subsequence, st))
+            ctx.check(ctx.lib.matm_fill_normal(ctx.h, dv["z"].data_ptr(), dv["z"].numel(), seed, 2 * subsequence + 1, st))
+        ctx.check(ctx.lib.matm_ar_generate(ctx.h, n_ext, n_cs, self.n_sample, dv["A"].data_ptr(), dv["B"].data_ptr(),
+                                           dv["esi"].data_ptr(), dv["csi"].data_ptr(), dv["buffer"].data_ptr(),
+                                           dv["z"].data_ptr(), st))
+        self._values_host = None
+        return self.values_device
+
+    @property
+    def values_device(self):
+        """(n_ext, n_cs) float64 view of the generated field on the device."""
+        return self._dev["buffer"][: self.n_extrusion]
+
+    @property
+    def values(self):
+        if self._values_host is None:
+            self._values_host = self.values_device.cpu().numpy()
+        return self._values_host
+
+
+class LazyCoords:
+    """The part of ``Coordinates`` the consumers of ``Atmosphere.coords`` read (``.t``, ``.az``, ``.el``), with the
+    (n_det, n_t) arrays evaluated only when asked for."""
+
+    def __init__(self, t, az_b, el_b, offsets):
+        self.t, self._az_b, self._el_b, self._offsets = t, az_b, el_b, offsets
+        self.shape = (len(offsets), len(t))
+
+    def _eval(self):
+        if not hasattr(self, "_az"):
+            self._az, self._el = host.offsets_to_az_el(self._offsets, self._az_b, self._el_b)
+        return self._az, self._el
+
+    @property
+    def az(self):
+        return self._eval()[0]
+
+    @property
+    def el(self):
+        return self._eval()[1]
+
+
+class Boresight:
+    def __init__(self, t, az, el):
+        self.t, self.az, self.el = np.asarray(t, dtype=float), np.asarray(az, dtype=float), np.asarray(el, dtype=float)
+        self.shape = self.az.shape
+
+    def downsample(self, timestep):
+        """coordinates.py:286-304: linear interpolation onto arange(t.min(), t.max(), timestep)."""
+        ds_t = np.arange(self.t.min(), self.t.max(), timestep)
+        kw = dict(axis=-1, bounds_error=False, fill_value="extrapolate")
+        return Boresight(ds_t, sp.interpolate.interp1d(self.t, self.az, **kw)(ds_t),
+                         sp.interpolate.interp1d(self.t, self.el, **kw)(ds_t))
+
+
+class Atmosphere:
+    """maria/atmosphere/atmosphere.py:31-380.  Same constructor arguments and attributes as the reference; offline
+    there are no ERA5 / ``am`` tables, so ``weather`` may also be a ready ``inputs.Weather`` and ``spectrum`` a ready
+    ``inputs.AtmosphericSpectrum`` (a dict ``weather`` is the reference's override, applied to the synthetic stand-in).
+
+    Opt-in keys (all have defaults, so the reference's call sites work unchanged):
+      device     CUDA device index                     precision  "fp32" (production) | "fp64" (validation)
+      noise      "host": the AR noise is drawn from ``rng`` on the host in the reference's order (validation mode)
+                 "philox": counter-based RNG on the device, keyed by ``seed``
+      rng        object with ``standard_normal(size)``; default the global ``np.random`` like the reference
+      geometry   "exact" | "fast" | "auto": footprint alignment on all points (reference) or on their 3-D hull
+    """
+
+    def __init__(self, model="2d", timestamp=None, region="princeton", altitude=None, weather=None,
+                 weather_quantiles=None, weather_source="era5", spectrum_source="am", pwv_rms_frac=0.03,
+                 max_height=5e3, timestep=None, interpolation_method="linear", disable_progress_bars=False, *,
+                 spectrum=None, device=0, precision="fp32", noise="host", seed=1234, rng=None, geometry="auto"):
+        if model not in SUPPORTED_MODELS_LIST:
+            raise ValueError(f"Invalid model '{model}'. Supported models are {SUPPORTED_MODELS_LIST}.")
+        if noise not in ("host", "philox"):
+            raise ValueError(f"Invalid noise mode '{noise}'. Supported: 'host', 'philox'.")
+        if interpolation_method != "linear":
+            raise ValueError("only interpolation_method='linear' is implemented on the device")
+        if precision not in _PRECISIONS:
+            raise ValueError(f"Invalid precision '{precision}'. Supported: fp32, fp64.")
+        if isinstance(weather, inputs.Weather):
+            self.weather = weather
+        else:
+            self.weather = inputs.make_weather(region, altitude or 0.0, pwv=(weather or {}).get("pwv"))
+        self.spectrum = spectrum if spectrum is not None else inputs.make_spectrum(region)
+        self.timestamp, self.region = timestamp, region
+        self.pwv_rms_frac = pwv_rms_frac  # stored, not forwarded: the reference does the same (atmosphere.py:67,86-94)
+        self.angular = False
+        self.model, self.max_height, self.timestep = model, max_height, timestep
+        self.interpolation_method = interpolation_method
+        self.disable_progress_bars = disable_progress_bars
+        self.device, self.precision, self.noise, self.seed = device, precision, noise, seed
+        self.rng = rng if rng is not None else np.random
+        self.geometry = geometry
+        self._initialized = False
+        self._generated = False
+
+    def __repr__(self):
+        return f"Atmosphere(model={self.model}, region={self.region}, pwv={self.weather.pwv:.3f} mm, device=cuda:{self.device})"
+
+    # ---------------------------------------------------------------------------------------------------------
+    def initialize(self, obs, bind=True):
+        """atmosphere.py:81-281: layer table, timestep, downsampled boresight, one AR process per layer.
+        ``bind=False`` stops after the host set-up (no device is touched; used by the CPU tests of the host logic)."""
+        dets = obs.instrument.dets
+        rng = self.rng
+        self.layers = host.generate_layers(dets, obs.boresight.el.min(), self.weather, obs.site.altitude, mode=self.model,
+                                           angular=self.angular, max_height=self.max_height)
+        L = self.layers
+        if self.timestep is None:  # :96-99
+            min_fwhm = host.gaussian_beam_angular_fwhm(dets.primary_size, self.max_height, dets.band_center).min()
+            self.timestep = max(1e-1, min_fwhm / (L["wind_speed"] / L["h"]).max())
+        self.boresight = obs.boresight.downsample(timestep=self.timestep)  # :101
+        n_t = len(self.boresight.t)
+        self.coords = LazyCoords(self.boresight.t, self.boresight.az, self.boresight.el, dets.offsets)  # :102-105
+        outer = dets.offsets[host.outer_detector_mask(dets.offsets)]  # :108-111
+        outer_az, outer_el = host.offsets_to_az_el(outer, self.boresight.az, self.boresight.el)
+
+        self.processes = {}
+        for process_index in sorted(np.unique(L["process_index"])):
+            t0 = ttime.monotonic()
+            idx = np.where(L["process_index"] == process_index)[0]
+            vx = L["wind_east"][idx][:, None] * np.ones(n_t)  # :149-154 (non-angular branch)
+            vy = L["wind_north"][idx][:, None] * np.ones(n_t)
+            w = L["absolute_humidity"][idx] * L["temperature"][idx] * L["divergence"][idx]
+            vx = (w[:, None] * vx).sum(axis=0) / w.sum()
+            vy = (w[:, None] * vy).sum(axis=0) / w.sum()
+            drift = np.cumsum(self.timestep * np.c_[vx, vy, np.zeros(n_t)][None], axis=-2)
+            hull_layers = idx[[0, -1]] if len(idx) > 1 else idx  # :161-162
+            pts = np.concatenate([(host.project_to_height(outer_az, outer_el, L["h"][li]) + drift)[None]
+                                  for li in hull_layers], axis=0).reshape(-1, 3)
+            pts[..., 2] += 1e-6 * rng.standard_normal(pts[..., 2].shape)  # :184-186
+            fast = self.geometry == "fast" or (self.geometry == "auto" and len(pts) > 400_000)
+            transform = host.aligning_transform(pts, (True, True, False), rng=rng, reduce_to_hull=fast)  # :191-194
+            tp = pts @ transform
+            min_tx, max_tx = tp[:, 0].min(), tp[:, 0].max()
+            lo_y, hi_y = tp[:, 1].min(), tp[:, 1].max()
+            sections, labels = [], []
+            for li in idx:  # :203-219
+                res = L["res"][li]
+                n_cs = int(np.maximum(2, (np.ptp(tp[:, 1]) + 2 * res) / res))
+                sections.append(np.stack([np.linspace(lo_y - res, hi_y + res, n_cs), L["h"][li] * np.ones(n_cs)]).T)
+                labels.extend(n_cs * [li])
+            res_min = L["res"].min()
+            extrusion = np.arange(min_tx - 2 * res_min, max_tx + 2 * res_min, res_min)  # :241-245
+            outer_scale = np.maximum(1e3, 300 + L["h"][hull_layers].mean() / 10)  # :247
+            kw = {"nu": 1 / 3, "r0": outer_scale} if self.model == "3d" else {"nu": 5 / 6, "r0": outer_scale}
+            process = AutoregressiveProcess(np.concatenate(sections, axis=0), extrusion, callback_kwargs=kw, jitter=1e-8)
+            process.layer_index = idx
+            process.labels = np.array(labels)
+            process.transform = transform
+            process.extrusion_res = np.gradient(extrusion).mean()
+            process.vx, process.vy = vx, vy
+            process.tp_bounds = (min_tx, max_tx, lo_y, hi_y)
+            for attempt, jitter in enumerate([1e-8, 1e-6, 1e-4]):  # :267-277 (the reference never applies `jitter`)
+                try:
+                    process.compute_covariance_matrices(rng)
+                    break
+                except np.linalg.LinAlgError:
+                    logger.debug(f"Singular covariance matrix with jitter={jitter}")
+                    if attempt == 2:
+                        raise np.linalg.LinAlgError("Covariance matrix was singular even with max jitter.")
+            self.processes[int(process_index)] = process
+            logger.debug(f"Constructed process {process_index} ({process.n_extrusion} x {process.n_cross_section}, "
+                         f"n_sample={process.n_sample}) in {ttime.monotonic() - t0:.2f} s")
+        self._obs = obs
+        if bind:
+            self._bind_device(obs)
+            self._initialized = True
+
+    # ---------------------------------------------------------------------------------------------------------
+    def _bind_device(self, obs):
+        """Create the device context and upload scan, detectors, band tables and the process matrices."""
+        ctx = self.ctx = DeviceContext(self.device, self.precision)
+        lib, dets = ctx.lib, obs.instrument.dets
+        bs, full = self.boresight, obs.boresight
+        az_a, el_a = _lib.f64(bs.az), _lib.f64(bs.el)
+        t_f, az_f, el_f = _lib.f64(full.t), _lib.f64(full.az), _lib.f64(full.el)
+        t_a = _lib.f64(bs.t)
+        ctx.check(lib.matm_set_scan(ctx.h, len(bs.t), _lib.dptr(t_a), float(self.timestep), _lib.dptr(az_a), _lib.dptr(el_a),
+                                    len(t_f), _lib.dptr(t_f), _lib.dptr(az_f), _lib.dptr(el_f)))
+        band_names = [b.name for b in dets.bands]
+        band_index = np.array([band_names.index(b) for b in dets.band_name], dtype=np.int32)
+        off_atm = _lib.f64(dets.offsets)
+        off_full = _lib.f64(getattr(obs, "offsets", dets.offsets))
+        mu = _lib.f64(dets.mueller00())
+        ctx.check(lib.matm_set_detectors(ctx.h, dets.n, _lib.dptr(off_atm), _lib.dptr(off_full), _lib.iptr(band_index),
+                                         _lib.dptr(mu), None))
+        self.set_bands(dets)
+        for p in self.processes.values():
+            p.bind(ctx)
+        self._layer_dev = {}
+
+    def set_bands(self, dets):
+        """Band-integrated lookup tables (band.py:235-255,264-300), evaluated on the device from the spectrum tables."""
+        ctx, s = self.ctx, self.spectrum
+        T, W, E, NU = (_lib.f64(a) for a in s.points)
+        pb = _lib.f64(np.stack([b.passband(s.side_nu) for b in dets.bands]))
+        factor = _lib.f64([0.5 if (~np.isnan(dets.gamma[dets.band_name == b.name])).any() else 1.0 for b in dets.bands])
+        em, op = _lib.f64(s._emission), _lib.f64(s._opacity)
+        self.cal_pwv = float(np.round(self.weather.pwv, 3))            # simulation.py:258-259 metadata, used by TOD.to
+        self.cal_T0 = float(np.round(self.weather.temperature[0], 3))
+        ctx.check(ctx.lib.matm_set_bands(ctx.h, len(dets.bands), len(T), len(W), len(E), len(NU), _lib.dptr(T), _lib.dptr(W),
+                                         _lib.dptr(E), _lib.dptr(NU), _lib.dptr(em), _lib.dptr(op), _lib.dptr(pb),
+                                         float(self.weather.temperature[0]), self.cal_T0, self.cal_pwv, _lib.dptr(factor)))
+
+    def set_gain(self, gain):
+        """Per-detector gain factors exp(gain_error N(0,1)) (simulation.py:239-241)."""
+        ctx, obs = self.ctx, self._obs
+        dets = obs.instrument.dets
+        band_names = [b.name for b in dets.bands]
+        band_index = np.array([band_names.index(b) for b in dets.band_name], dtype=np.int32)
+        off_atm, off_full = _lib.f64(dets.offsets), _lib.f64(getattr(obs, "offsets", dets.offsets))
+        mu, g = _lib.f64(dets.mueller00()), _lib.f64(gain)
+        ctx.check(ctx.lib.matm_set_detectors(ctx.h, dets.n, _lib.dptr(off_atm), _lib.dptr(off_full), _lib.iptr(band_index),
+                                             _lib.dptr(mu), _lib.dptr(g)))
+
+    # ---------------------------------------------------------------------------------------------------------
+    def generate(self):
+        """Stage 1: run every AR process and beam-smooth every layer on the device (atmosphere.py:299-307,328-344)."""
+        if not self._initialized:
+            raise RuntimeError("Atmosphere must be initialized with a simulation.")
+        ctx, L = self.ctx, self.layers
+        tc = ctx.torch
+        dets = self._obs.instrument.dets
+        for k, process in self.processes.items():
+            if self.noise == "host":
+                process.run(rng=self.rng)
+            else:
+                process.run(seed=self.seed, subsequence=k)
+        st = ctx.stream_ptr()
+        descs = (_lib.LayerDesc * len(L["h"]))()
+        keep = []
+        n_layers = 0
+        for k, process in self.processes.items():
+            vx, vy = _lib.f64(process.vx), _lib.f64(process.vy)
+            keep += [vx, vy]
+            for li in process.layer_index:
+                cols = np.where(process.labels == li)[0]
+                col0, n_cols = int(cols[0]), len(cols)
+                beam_sigma = host.gaussian_beam_physical_fwhm(dets.primary_size, L["z"][li], dets.band_center).mean() / 2.355
+                sig_e, sig_x = beam_sigma / process.extrusion_res, beam_sigma / L["res"][li]  # :328-339
+                if li not in self._layer_dev:
+                    self._layer_dev[li] = (ctx.empty((process.n_extrusion, n_cols)),
+                                           ctx.empty((process.n_extrusion, n_cols), tc.float64))
+                out, scratch = self._layer_dev[li]
+                ctx.check(ctx.lib.matm_smooth_layer(ctx.h, process.values_device.data_ptr(), process.n_extrusion,
+                                                    process.n_cross_section, col0, n_cols, float(sig_e), float(sig_x),
+                                                    out.data_ptr(), scratch.data_ptr(), st))
+                d = descs[n_layers]
+                d.data_dev, d.n_ext, d.n_cs = out.data_ptr(), process.n_extrusion, n_cols
+                d.h, d.pwv_rms = float(L["h"][li]), float(L["pwv_rms"][li])
+                d.transform = (C.c_double * 9)(*np.asarray(process.transform, dtype=float).ravel())
+                d.ext0, d.ext_step = float(process.extrusion[0]), float(process.extrusion_res)
+                xs = process.cross_section[cols, 0]
+                d.cs0, d.cs_last = float(xs[0]), float(xs[-1])
+                d.vx_host, d.vy_host = _lib.dptr(vx), _lib.dptr(vy)
+                n_layers += 1
+        if not getattr(self, "_layers_set", False):
+            ctx.check(ctx.lib.matm_set_layers(ctx.h, n_layers, descs, float(self.weather.pwv)))
+            self._layers_set = True
+        self._generated = True
+
+    def smoothed_layer(self, li):
+        """Beam-smoothed layer ``li`` as a host array (validation helper)."""
+        return self._layer_dev[li][0].cpu().numpy()
+
+    def zenith_pwv_device(self, det0=0, n_det=None):
+        """(n_det, n_t_atm) float64 zenith_scaled_pwv on the device for a detector range (atmosphere.py:309-373)."""
+        ctx = self.ctx
+        n_det = self._obs.instrument.dets.n - det0 if n_det is None else n_det
+        out = ctx.empty((n_det, len(self.boresight.t)), ctx.torch.float64)
+        ctx.check(ctx.lib.matm_zenith_pwv(ctx.h, det0, n_det, out.data_ptr(), ctx.stream_ptr()))
+        return out
+
+    def simulate_pwv(self, instrument=None):
+        """atmosphere.py:293-380.  Generates the layers; ``zenith_scaled_pwv`` is evaluated when read."""
+        if not self._initialized:
+            raise RuntimeError("Atmosphere must be initialized with a simulation.")
+        self.generate()
+        self.__dict__.pop("_zpwv_host", None)
+
+    @property
+    def zenith_scaled_pwv(self):
+        if not self._generated:
+            raise RuntimeError("simulate_pwv() has not been called.")
+        if "_zpwv_host" not in self.__dict__:
+            z = self.zenith_pwv_device().cpu().numpy()
+            self.check_flags()
+            self._zpwv_host = z
+        return self._zpwv_host
+
+    def check_flags(self):
+        """Raise what the reference raises when a line of sight leaves a layer (atmosphere.py:368-369)."""
+        st, layer, det, sample = self.ctx.raise_on_flags()
+        if st == _lib.ERR_OUT_OF_GRID:
+            k = int(self.layers["process_index"][layer]) if layer < len(self.layers["h"]) else -1
+            raise RuntimeError(f"Layer {layer} in process {k} introduced nans into PWV simulation "
+                               f"(detector {det}, sample {sample}).")
+        return st

@@ -1,0 +1,122 @@
+// Shared declarations of libmaria_atm.so (handle state, device-side descriptors, error helpers).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/maria_atm.h"
+
+#define MATM_ABI_VERSION 1
+
+// Device-side layer descriptor: everything the sampler needs per layer, in cell units.
+struct LayerDev {
+  const void* data;   // (n_ext, n_cs) row-major, float or double
+  const double* base; // (n_t_atm, 2): boresight position in the layer grid, in cells (f64)
+  int n_ext, n_cs;
+  double D[4];        // 2x2: cells per unit of (pp_d - pp_b): [x<-x, x<-y, y<-x, y<-y]
+  double pwv_rms;
+};
+
+struct SynthParams {
+  int n_layers;
+  LayerDev layers[MATM_MAX_LAYERS];
+  double pwv0;
+  // scan
+  int n_t_atm;
+  int64_t n_t;
+  double t_atm0, timestep;
+  const double* bore_atm;  // (n_t_atm, 4): ce, se, ca, sa  (e = el_b - pi/2, a = az_b)
+  const double* bore_full; // (n_t, 2): ce, se at the full rate
+  const double* t_full;    // (n_t,)
+  const int64_t* jstart;   // (n_t_atm + 1,): first full-rate sample with t >= t_atm[k]; jstart[n_t_atm] = n_t
+  const double* t_atm;     // (n_t_atm,): the knot times exactly as np.arange produced them
+  const double* spl;       // (n_t_atm, 5): not-a-knot cubic spline system in units of `timestep`:
+                           //   [0] 1/h_k  [1] h_k^2/6 (interval k);  [2] w_k  [3] a_k w_k  [4] c'_k (row k, Thomas)
+  // detectors
+  int64_t n_det;
+  const double* det_atm;   // (n_det, 4): u, Y, w-1, unused   with the atmosphere's offsets
+  const double* det_full;  // (n_det, 2): u, w                with the rolled offsets
+  const int32_t* band_index;
+  const double* mueller00;
+  const double* gain;
+  // bands
+  int n_bands, npwv, nel;
+  const double* side_pwv;  // (npwv,)
+  const double* side_el;   // (nel,)
+  const double* G2;        // (n_bands, npwv, nel) emission grid folded at T0 [pW]
+  const double* H1;        // (n_bands, nel) transmission integral folded at (cal_T0, cal_pwv), times factor*k_B*1e12
+  int table_ok;            // 0 if T0 / cal_T0 / cal_pwv left the table (results are NaN, as the reference)
+  int* flags;              // [0] = status bits, [1] = layer, [2..3] = det (lo, hi), [4..5] = sample (lo, hi)
+};
+
+struct matm_handle {
+  int device = 0;
+  int dtype = MATM_F32;
+  std::string err;
+  int64_t launches = 0;
+  int sm_count = 148;
+  bool have_scan = false, have_layers = false, have_dets = false, have_bands = false;
+  SynthParams P;
+  // owned device arrays
+  double *bore_atm = nullptr, *bore_full = nullptr, *t_full = nullptr;
+  int64_t* jstart = nullptr;
+  double *t_atm = nullptr, *spl = nullptr;
+  double* layer_base[MATM_MAX_LAYERS] = {};
+  double *det_atm = nullptr, *det_full = nullptr, *mueller00 = nullptr, *gain = nullptr;
+  int32_t* band_index = nullptr;
+  double *side_pwv = nullptr, *side_el = nullptr, *G2 = nullptr, *H1 = nullptr;
+  int* flags = nullptr;
+  std::vector<double> az_atm_host, el_atm_host;
+  // e2e staging
+  void* stage_dev[2] = {nullptr, nullptr};
+  void* stage_pinned[2] = {nullptr, nullptr};
+  size_t stage_bytes = 0;
+  cudaStream_t stage_stream[2] = {nullptr, nullptr};
+  cudaEvent_t stage_done[2] = {nullptr, nullptr};
+};
+
+#define MATM_CHECK_HANDLE(h) \
+  if (!(h)) return MATM_ERR_ARG;
+
+#define MATM_CUDA(h, call)                                                                      \
+  do {                                                                                          \
+    cudaError_t e__ = (call);                                                                   \
+    if (e__ != cudaSuccess) {                                                                   \
+      (h)->err = std::string(#call) + ": " + cudaGetErrorString(e__) + " (" + __FILE__ + ":" +  \
+                 std::to_string(__LINE__) + ")";                                                \
+      return MATM_ERR_CUDA;                                                                     \
+    }                                                                                           \
+  } while (0)
+
+#define MATM_FAIL_ARG(h, msg) \
+  do {                        \
+    (h)->err = (msg);         \
+    return MATM_ERR_ARG;      \
+  } while (0)
+
+#define MATM_LAUNCHED(h)                         \
+  do {                                           \
+    (h)->launches++;                             \
+    MATM_CUDA(h, cudaGetLastError());            \
+  } while (0)
+
+template <typename T>
+static inline int matm_upload(matm_handle* h, T** dst, const T* src_host, size_t n) {
+  if (*dst) {
+    MATM_CUDA(h, cudaFree(*dst));
+    *dst = nullptr;
+  }
+  if (n == 0) return MATM_OK;
+  MATM_CUDA(h, cudaMalloc((void**)dst, n * sizeof(T)));
+  if (src_host) MATM_CUDA(h, cudaMemcpy(*dst, src_host, n * sizeof(T), cudaMemcpyHostToDevice));
+  return MATM_OK;
+}
+
+static inline int matm_set_device(matm_handle* h) {
+  MATM_CUDA(h, cudaSetDevice(h->device));
+  return MATM_OK;
+}

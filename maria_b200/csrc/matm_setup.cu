@@ -1,0 +1,337 @@
+// Set-up entry points: scan, layers, detectors, band tables.  Small host arrays are uploaded and the derived
+// per-time / per-detector / per-band constants are evaluated on the device in float64.
+#include "matm_common.cuh"
+
+#define K_B 1.380649e-23
+
+// ---- scan ------------------------------------------------------------------------------------------------
+// maria/coords/transforms.py:10-29: q = (sin r cos p + i cos r) * exp(i (el_b - pi/2)); az = atan2(sin r sin p, Re q) + az_b
+__global__ void bore_atm_kernel(const double* __restrict__ az, const double* __restrict__ el, double* __restrict__ out, int n) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  double se, ce, sa, ca;
+  sincos(el[k] - M_PI / 2, &se, &ce);
+  sincos(az[k], &sa, &ca);
+  out[4 * k + 0] = ce;
+  out[4 * k + 1] = se;
+  out[4 * k + 2] = ca;
+  out[4 * k + 3] = sa;
+}
+
+__global__ void bore_full_kernel(const double* __restrict__ el, double* __restrict__ out, int64_t n) {
+  int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  double se, ce;
+  sincos(el[j] - M_PI / 2, &se, &ce);
+  out[2 * j + 0] = ce;
+  out[2 * j + 1] = se;
+}
+
+__host__ __device__ __forceinline__ int interval_of(double t, double t0, double ts, int n_atm) {
+  int i = (int)floor((t - t0) / ts);
+  int hi = n_atm - 2;
+  return i < 0 ? 0 : (i > hi ? hi : i);
+}
+
+// jstart[k] = first full-rate sample whose interpolation interval (sim/atmosphere.py:30-37,73-80) is >= k
+__global__ void jstart_kernel(const double* __restrict__ t, int64_t n_t, double t0, double ts, int n_atm,
+                              int64_t* __restrict__ jstart) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n_atm) return;
+  if (k >= n_atm - 1) {
+    jstart[k] = n_t;
+    return;
+  }
+  int64_t lo = 0, hi = n_t;  // first j with interval_of(t[j]) >= k
+  while (lo < hi) {
+    int64_t mid = (lo + hi) / 2;
+    if (interval_of(t[mid], t0, ts, n_atm) >= k)
+      hi = mid;
+    else
+      lo = mid + 1;
+  }
+  jstart[k] = lo;
+}
+
+extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, double t_atm0, double timestep, const double* az_atm_host,
+                             const double* el_atm_host, int64_t n_t, const double* t_host, const double* az_host,
+                             const double* el_host) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (n_t_atm < 2 || n_t < 1 || !(timestep > 0)) MATM_FAIL_ARG(h, "matm_set_scan: need n_t_atm >= 2, n_t >= 1, timestep > 0");
+  if (!az_atm_host || !el_atm_host || !t_host || !el_host) MATM_FAIL_ARG(h, "matm_set_scan: null pointer");
+  (void)az_host;  // the full-rate azimuth does not enter the path (only the elevation does, tod.py:126-133)
+  double *az_d = nullptr, *el_d = nullptr, *elf_d = nullptr;
+  int rc;
+  if ((rc = matm_upload(h, &az_d, az_atm_host, (size_t)n_t_atm))) return rc;
+  if ((rc = matm_upload(h, &el_d, el_atm_host, (size_t)n_t_atm))) return rc;
+  if ((rc = matm_upload(h, &elf_d, el_host, (size_t)n_t))) return rc;
+  if ((rc = matm_upload(h, &h->bore_atm, (const double*)nullptr, (size_t)n_t_atm * 4))) return rc;
+  if ((rc = matm_upload(h, &h->bore_full, (const double*)nullptr, (size_t)n_t * 2))) return rc;
+  if ((rc = matm_upload(h, &h->t_full, t_host, (size_t)n_t))) return rc;
+  if ((rc = matm_upload(h, &h->jstart, (const int64_t*)nullptr, (size_t)n_t_atm + 1))) return rc;
+  bore_atm_kernel<<<(n_t_atm + 255) / 256, 256>>>(az_d, el_d, h->bore_atm, n_t_atm);
+  MATM_LAUNCHED(h);
+  bore_full_kernel<<<(unsigned)((n_t + 255) / 256), 256>>>(elf_d, h->bore_full, n_t);
+  MATM_LAUNCHED(h);
+  jstart_kernel<<<(n_t_atm + 1 + 255) / 256, 256>>>(h->t_full, n_t, t_atm0, timestep, n_t_atm, h->jstart);
+  MATM_LAUNCHED(h);
+  MATM_CUDA(h, cudaDeviceSynchronize());
+  cudaFree(az_d);
+  cudaFree(el_d);
+  cudaFree(elf_d);
+  SynthParams& P = h->P;
+  P.n_t_atm = n_t_atm;
+  P.n_t = n_t;
+  P.t_atm0 = t_atm0;
+  P.timestep = timestep;
+  P.bore_atm = h->bore_atm;
+  P.bore_full = h->bore_full;
+  P.t_full = h->t_full;
+  P.jstart = h->jstart;
+  h->have_scan = true;
+  h->have_layers = false;  // layer bases depend on the scan
+  return MATM_OK;
+}
+
+// ---- layers ----------------------------------------------------------------------------------------------
+// base[k] = ((h * pp_b[k] + cumsum(timestep * v)[k]) @ T - grid origin) / grid step   (atmosphere.py:318-319,346-347)
+__global__ void layer_base_kernel(const double* __restrict__ bore_atm, const double* __restrict__ vx,
+                                  const double* __restrict__ vy, int n, double timestep, double hgt, const double* T9,
+                                  double ext0, double ext_step, double cs0, double cs_step, double* __restrict__ base) {
+  // inclusive cumulative sum, sequential like np.cumsum, one thread per component
+  if (threadIdx.x < 2) {
+    const double* v = threadIdx.x == 0 ? vx : vy;
+    double acc = 0.0;
+    for (int k = 0; k < n; k++) {
+      acc += timestep * v[k];
+      base[2 * k + threadIdx.x] = acc;
+    }
+  }
+  __syncthreads();
+  for (int k = threadIdx.x; k < n; k += blockDim.x) {
+    double ce = bore_atm[4 * k + 0], se = bore_atm[4 * k + 1], ca = bore_atm[4 * k + 2], sa = bore_atm[4 * k + 3];
+    // boresight direction (cos el cos az, cos el sin az, sin el) with cos el = -se, sin el = ce
+    double px = hgt * ((-se * ca) / ce) + base[2 * k + 0];
+    double py = hgt * ((-se * sa) / ce) + base[2 * k + 1];
+    double pz = hgt;
+    double qx = px * T9[0] + py * T9[3] + pz * T9[6];
+    double qy = px * T9[1] + py * T9[4] + pz * T9[7];
+    base[2 * k + 0] = (qx - ext0) / ext_step;
+    base[2 * k + 1] = (qy - cs0) / cs_step;
+  }
+}
+
+extern "C" int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_desc* L, double pwv0) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (!h->have_scan) MATM_FAIL_ARG(h, "matm_set_layers: call matm_set_scan first");
+  if (n_layers < 0 || n_layers > MATM_MAX_LAYERS || (n_layers && !L)) MATM_FAIL_ARG(h, "matm_set_layers: bad layer count");
+  SynthParams& P = h->P;
+  const int n = P.n_t_atm;
+  double *vx_d = nullptr, *vy_d = nullptr, *T_d = nullptr;
+  int rc;
+  for (int l = 0; l < n_layers; l++) {
+    const matm_layer_desc& d = L[l];
+    if (!d.data_dev || d.n_ext < 2 || d.n_cs < 2 || !d.vx_host || !d.vy_host || !(d.ext_step > 0) || !(d.cs_last > d.cs0))
+      MATM_FAIL_ARG(h, "matm_set_layers: bad layer descriptor");
+    if ((rc = matm_upload(h, &vx_d, d.vx_host, (size_t)n))) return rc;
+    if ((rc = matm_upload(h, &vy_d, d.vy_host, (size_t)n))) return rc;
+    if ((rc = matm_upload(h, &T_d, d.transform, (size_t)9))) return rc;
+    if ((rc = matm_upload(h, &h->layer_base[l], (const double*)nullptr, (size_t)n * 2))) return rc;
+    const double cs_step = (d.cs_last - d.cs0) / (d.n_cs - 1);
+    layer_base_kernel<<<1, 256>>>(h->bore_atm, vx_d, vy_d, n, P.timestep, d.h, T_d, d.ext0, d.ext_step, d.cs0, cs_step,
+                                  h->layer_base[l]);
+    MATM_LAUNCHED(h);
+    MATM_CUDA(h, cudaDeviceSynchronize());
+    LayerDev& o = P.layers[l];
+    o.data = d.data_dev;
+    o.base = h->layer_base[l];
+    o.n_ext = d.n_ext;
+    o.n_cs = d.n_cs;
+    o.D[0] = d.h * d.transform[0] / d.ext_step;
+    o.D[1] = d.h * d.transform[3] / d.ext_step;
+    o.D[2] = d.h * d.transform[1] / cs_step;
+    o.D[3] = d.h * d.transform[4] / cs_step;
+    o.pwv_rms = d.pwv_rms;
+  }
+  cudaFree(vx_d);
+  cudaFree(vy_d);
+  cudaFree(T_d);
+  P.n_layers = n_layers;
+  P.pwv0 = pwv0;
+  h->have_layers = true;
+  return MATM_OK;
+}
+
+// ---- detectors -------------------------------------------------------------------------------------------
+__global__ void det_kernel(const double* __restrict__ off_atm, const double* __restrict__ off_full, int64_t n,
+                           double* __restrict__ det_atm, double* __restrict__ det_full) {
+  int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (d >= n) return;
+  {
+    double dx = off_atm[2 * d], dy = off_atm[2 * d + 1];
+    double r = sqrt(dx * dx + dy * dy), p = atan2(-dx, -dy);
+    double sr, cr, sp, cp, sh = sin(0.5 * r);
+    sincos(r, &sr, &cr);
+    sincos(p, &sp, &cp);
+    det_atm[4 * d + 0] = sr * cp;
+    det_atm[4 * d + 1] = sr * sp;
+    det_atm[4 * d + 2] = -2.0 * sh * sh;  // cos r - 1 without cancellation
+    det_atm[4 * d + 3] = cr;
+  }
+  {
+    double dx = off_full[2 * d], dy = off_full[2 * d + 1];
+    double r = sqrt(dx * dx + dy * dy), p = atan2(-dx, -dy);
+    det_full[2 * d + 0] = sin(r) * cos(p);
+    det_full[2 * d + 1] = cos(r);
+  }
+}
+
+extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* offsets_atm_host,
+                                  const double* offsets_full_host, const int32_t* band_index_host,
+                                  const double* mueller00_host, const double* gain_host) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (n_det < 1 || !offsets_atm_host || !offsets_full_host || !band_index_host || !mueller00_host)
+    MATM_FAIL_ARG(h, "matm_set_detectors: bad arguments");
+  double *oa = nullptr, *of = nullptr;
+  int rc;
+  if ((rc = matm_upload(h, &oa, offsets_atm_host, (size_t)n_det * 2))) return rc;
+  if ((rc = matm_upload(h, &of, offsets_full_host, (size_t)n_det * 2))) return rc;
+  if ((rc = matm_upload(h, &h->det_atm, (const double*)nullptr, (size_t)n_det * 4))) return rc;
+  if ((rc = matm_upload(h, &h->det_full, (const double*)nullptr, (size_t)n_det * 2))) return rc;
+  if ((rc = matm_upload(h, &h->band_index, band_index_host, (size_t)n_det))) return rc;
+  if ((rc = matm_upload(h, &h->mueller00, mueller00_host, (size_t)n_det))) return rc;
+  std::vector<double> ones;
+  if (!gain_host) {
+    ones.assign((size_t)n_det, 1.0);
+    gain_host = ones.data();
+  }
+  if ((rc = matm_upload(h, &h->gain, gain_host, (size_t)n_det))) return rc;
+  det_kernel<<<(unsigned)((n_det + 255) / 256), 256>>>(oa, of, n_det, h->det_atm, h->det_full);
+  MATM_LAUNCHED(h);
+  MATM_CUDA(h, cudaDeviceSynchronize());
+  cudaFree(oa);
+  cudaFree(of);
+  SynthParams& P = h->P;
+  P.n_det = n_det;
+  P.det_atm = h->det_atm;
+  P.det_full = h->det_full;
+  P.band_index = h->band_index;
+  P.mueller00 = h->mueller00;
+  P.gain = h->gain;
+  h->have_dets = true;
+  return MATM_OK;
+}
+
+// ---- band tables -----------------------------------------------------------------------------------------
+// trapezoid over nu of f(table[..., nu]) * passband[nu]  (band.py:248-253,272-280)
+__device__ double band_integral(const double* __restrict__ tab, const double* __restrict__ pb,
+                                const double* __restrict__ nu, int nnu, bool transmission) {
+  double acc = 0.0;
+  double prev = transmission ? pb[0] * exp(-tab[0]) : tab[0] * pb[0];
+  for (int i = 1; i < nnu; i++) {
+    double cur = transmission ? pb[i] * exp(-tab[i]) : tab[i] * pb[i];
+    acc += (nu[i] - nu[i - 1]) * (cur + prev) / 2.0;
+    prev = cur;
+  }
+  return acc;
+}
+
+// jax RegularGridInterpolator index / weight on one axis (SURVEY 8a notes); returns false when out of bounds
+__host__ __device__ inline bool axis_locate(const double* g, int n, double x, int* idx, double* w) {
+  int lo = 0, hi = n;  // searchsorted(g, x), side="left"
+  while (lo < hi) {
+    int mid = (lo + hi) / 2;
+    if (g[mid] < x)
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  int i = lo - 1;
+  i = i < 0 ? 0 : (i > n - 2 ? n - 2 : i);
+  *idx = i;
+  *w = (x - g[i]) / (g[i + 1] - g[i]);
+  return !(x < g[0] || x > g[n - 1]) && (x == x);
+}
+
+__global__ void fold_tables_kernel(const double* __restrict__ emission, const double* __restrict__ opacity,
+                                   const double* __restrict__ passband, const double* __restrict__ nu, int n_bands,
+                                   int nT, int npwv, int nel, int nnu, int iT, double wT, int iTc, double wTc, int iPc,
+                                   double wPc, const double* __restrict__ cal_scale, double* __restrict__ G2,
+                                   double* __restrict__ H1) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  int total_g = n_bands * npwv * nel;
+  if (e < total_g) {
+    int b = e / (npwv * nel), w = (e / nel) % npwv, el = e % nel;
+    const double* pb = passband + (size_t)b * nnu;
+    double g0 = band_integral(emission + (((size_t)iT * npwv + w) * nel + el) * nnu, pb, nu, nnu, false);
+    double g1 = band_integral(emission + (((size_t)(iT + 1) * npwv + w) * nel + el) * nnu, pb, nu, nnu, false);
+    G2[e] = 1e12 * K_B * (g0 * (1.0 - wT) + g1 * wT);
+  } else if (e < total_g + n_bands * nel) {
+    int f = e - total_g;
+    int b = f / nel, el = f % nel;
+    const double* pb = passband + (size_t)b * nnu;
+    double acc = 0.0;
+    for (int dt = 0; dt < 2; dt++)
+      for (int dp = 0; dp < 2; dp++) {
+        double v = band_integral(opacity + (((size_t)(iTc + dt) * npwv + (iPc + dp)) * nel + el) * nnu, pb, nu, nnu, true);
+        acc += v * (dt ? wTc : 1.0 - wTc) * (dp ? wPc : 1.0 - wPc);
+      }
+    H1[f] = acc * cal_scale[b];
+  }
+}
+
+extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int nel, int nnu, const double* side_T_host,
+                              const double* side_pwv_host, const double* side_el_host, const double* side_nu_host,
+                              const double* emission_host, const double* opacity_host, const double* passband_host,
+                              double T0, double cal_T0, double cal_pwv, const double* cal_factor_host) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (n_bands < 1 || n_bands > MATM_MAX_BANDS || nT < 2 || npwv < 2 || nel < 2 || nnu < 2)
+    MATM_FAIL_ARG(h, "matm_set_bands: bad table shape");
+  if (!side_T_host || !side_pwv_host || !side_el_host || !side_nu_host || !emission_host || !opacity_host ||
+      !passband_host || !cal_factor_host)
+    MATM_FAIL_ARG(h, "matm_set_bands: null pointer");
+  const size_t ntab = (size_t)nT * npwv * nel * nnu;
+  double *em = nullptr, *op = nullptr, *pb = nullptr, *nu = nullptr, *cs = nullptr;
+  int rc;
+  if ((rc = matm_upload(h, &em, emission_host, ntab))) return rc;
+  if ((rc = matm_upload(h, &op, opacity_host, ntab))) return rc;
+  if ((rc = matm_upload(h, &pb, passband_host, (size_t)n_bands * nnu))) return rc;
+  if ((rc = matm_upload(h, &nu, side_nu_host, (size_t)nnu))) return rc;
+  std::vector<double> scale((size_t)n_bands);
+  for (int b = 0; b < n_bands; b++) scale[b] = cal_factor_host[b] * K_B * 1e12;  // K_RJ = pW / (factor k_B 1e12 H)
+  if ((rc = matm_upload(h, &cs, scale.data(), (size_t)n_bands))) return rc;
+  if ((rc = matm_upload(h, &h->side_pwv, side_pwv_host, (size_t)npwv))) return rc;
+  if ((rc = matm_upload(h, &h->side_el, side_el_host, (size_t)nel))) return rc;
+  if ((rc = matm_upload(h, &h->G2, (const double*)nullptr, (size_t)n_bands * npwv * nel))) return rc;
+  if ((rc = matm_upload(h, &h->H1, (const double*)nullptr, (size_t)n_bands * nel))) return rc;
+  int iT, iTc, iPc;
+  double wT, wTc, wPc;
+  bool ok = axis_locate(side_T_host, nT, T0, &iT, &wT);
+  bool okc = axis_locate(side_T_host, nT, cal_T0, &iTc, &wTc);
+  okc = axis_locate(side_pwv_host, npwv, cal_pwv, &iPc, &wPc) && okc;
+  int total = n_bands * npwv * nel + n_bands * nel;
+  fold_tables_kernel<<<(total + 127) / 128, 128>>>(em, op, pb, nu, n_bands, nT, npwv, nel, nnu, iT, wT, iTc, wTc, iPc, wPc,
+                                                   cs, h->G2, h->H1);
+  MATM_LAUNCHED(h);
+  MATM_CUDA(h, cudaDeviceSynchronize());
+  cudaFree(em);
+  cudaFree(op);
+  cudaFree(pb);
+  cudaFree(nu);
+  cudaFree(cs);
+  SynthParams& P = h->P;
+  P.n_bands = n_bands;
+  P.npwv = npwv;
+  P.nel = nel;
+  P.side_pwv = h->side_pwv;
+  P.side_el = h->side_el;
+  P.G2 = h->G2;
+  P.H1 = h->H1;
+  P.table_ok = (ok ? 1 : 0) | (okc ? 2 : 0);
+  h->have_bands = true;
+  return MATM_OK;
+}

@@ -1,0 +1,345 @@
+// The detector x time stages: a6/a7/a9 (line-of-sight sampling), a10 (linear upsample), and the fused
+// a6..a14 synthesis kernel (sampling -> emission lookup -> cubic not-a-knot upsample -> gain -> pW->K_RJ).
+#include "matm_synth.cuh"
+
+#define DT 32          // detectors per tile (one lane per detector in the atmosphere-rate phase)
+#define SY_THREADS 256
+
+template <typename R>
+struct Tile {
+  static constexpr int KT = sizeof(R) == 4 ? 128 : 64;   // spline intervals per tile
+  static constexpr int HALO = sizeof(R) == 4 ? 12 : 24;  // extra knots each side; the error of the artificial
+                                                         // boundary decays as (2 - sqrt 3)^HALO
+  static constexpr int W = KT + 1 + 2 * HALO;            // knots in the window
+  static constexpr int WP = W + 1;                       // padded row length (bank-conflict free)
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// zenith_scaled_pwv at the atmosphere rate (atmosphere.py:293-380), float64 output
+// ---------------------------------------------------------------------------------------------------------
+template <typename R>
+__global__ void __launch_bounds__(SY_THREADS) zenith_pwv_kernel(const __grid_constant__ SynthParams P, int64_t det0,
+                                                                int64_t n_det, double* __restrict__ out) {
+  constexpr int W = 128;
+  __shared__ Knot<R> knots[W];
+  extern __shared__ __align__(16) unsigned char dyn[];
+  LayerKnot<R>* lk = reinterpret_cast<LayerKnot<R>*>(dyn);
+  const int n_ttiles = (P.n_t_atm + W - 1) / W;
+  const int64_t dtile = blockIdx.x / n_ttiles;
+  const int ttile = blockIdx.x % n_ttiles;
+  const int wa = ttile * W, Wn = min(W, P.n_t_atm - wa);
+  load_window<R>(P, wa, Wn, W, knots, lk);
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t d = dtile * DT + lane;
+  if (d >= n_det) return;
+  const double* da = P.det_atm + 4 * (det0 + d);
+  const R u = (R)da[0], Y = (R)da[1], wm1 = (R)da[2];
+  for (int k = warp; k < Wn; k += SY_THREADS / 32) {
+    R sin_el;
+    R z = sample_zenith_pwv<R>(P, u, Y, wm1, knots[k], lk + k, W, det0 + d, wa + k, &sin_el);
+    out[d * P.n_t_atm + wa + k] = (double)z;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// a10: scipy interp1d(kind="linear", fill_value="extrapolate") along time (sim/atmosphere.py:30-37)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) upsample_linear_kernel(const __grid_constant__ SynthParams P,
+                                                              const double* __restrict__ in, int64_t n_det,
+                                                              double* __restrict__ out) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= P.n_t) return;
+  const double t = P.t_full[j];
+  int i = (int)floor((t - P.t_atm0) / P.timestep);
+  i = min(max(i, 0), P.n_t_atm - 2);
+  const double x0 = P.t_atm0 + i * P.timestep, x1 = P.t_atm0 + (i + 1) * P.timestep;
+  const double s = (t - x0) / (x1 - x0);
+  for (int64_t d = blockIdx.y; d < n_det; d += gridDim.y) {
+    const double y0 = in[d * P.n_t_atm + i], y1 = in[d * P.n_t_atm + i + 1];
+    out[d * P.n_t + j] = y0 + s * (y1 - y0);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// The fused kernel.  One CTA = DT detectors x KT spline intervals.
+//   phase 1: loading [pW] at the window's knots (lane = detector, warp strides over knots)   -> smem y
+//   phase 2: second derivatives of the interpolating cubic spline by a windowed Thomas solve -> smem m
+//   phase 3: evaluate at the full-rate samples of the tile, gain, calibration, one store per sample
+// ---------------------------------------------------------------------------------------------------------
+template <typename R>
+__global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant__ SynthParams P, int64_t det0,
+                                                           int64_t n_det, R* __restrict__ out, int units,
+                                                           int apply_gain) {
+  using T = Tile<R>;
+  extern __shared__ __align__(16) unsigned char dyn[];
+  R* y = reinterpret_cast<R*>(dyn);                       // [DT][WP]
+  R* m = y + DT * T::WP;                                  // [DT][WP]
+  R* cprime = m + DT * T::WP;                             // [W] Thomas coefficients
+  Knot<R>* knots = reinterpret_cast<Knot<R>*>(cprime + T::W);
+  LayerKnot<R>* lk = reinterpret_cast<LayerKnot<R>*>(knots + T::W);  // [n_layers][W]
+  __shared__ R dc_u[DT], dc_w[DT], dc_gain[DT];
+  __shared__ int dc_band[DT];
+
+  const int n = P.n_t_atm;
+  const int n_int = n - 1;  // spline intervals
+  const int n_ttiles = (n_int + T::KT - 1) / T::KT;
+  const int64_t dtile = blockIdx.x / n_ttiles;
+  const int ttile = blockIdx.x % n_ttiles;
+  const int k0 = ttile * T::KT, k1 = min(k0 + T::KT, n_int);  // intervals [k0, k1), knots k0..k1
+  const int wa = max(0, k0 - T::HALO), wb = min(n - 1, k1 + T::HALO);
+  const int Wn = wb - wa + 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t dbase = dtile * DT;  // relative to det0
+  const int nd = (int)min((int64_t)DT, n_det - dbase);
+
+  load_window<R>(P, wa, Wn, T::W, knots, lk);
+  if (threadIdx.x < DT) {
+    int dd = threadIdx.x;
+    if (dd < nd) {
+      const int64_t d = det0 + dbase + dd;
+      dc_u[dd] = (R)P.det_full[2 * d];
+      dc_w[dd] = (R)P.det_full[2 * d + 1];
+      dc_gain[dd] = apply_gain ? (R)P.gain[d] : (R)1;
+      dc_band[dd] = P.band_index[d];
+    }
+  }
+  if (threadIdx.x == 0) {
+    // forward-elimination coefficients of the (1, 4, 1) system: c'_1 = 1/4, c'_k = 1 / (4 - c'_{k-1})
+    R c = (R)0.25;
+    cprime[0] = c;
+    for (int k = 1; k < T::W; k++) {
+      c = (R)1 / ((R)4 - c);
+      cprime[k] = c;
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 1 ----
+  if (lane < nd) {
+    const int64_t d = det0 + dbase + lane;
+    const double* da = P.det_atm + 4 * d;
+    const R u = (R)da[0], Y = (R)da[1], wm1 = (R)da[2];
+    const int band = P.band_index[d];
+    const R mu = (R)P.mueller00[d];
+    for (int k = warp; k < Wn; k += SY_THREADS / 32) {
+      R sin_el;
+      R z = sample_zenith_pwv<R>(P, u, Y, wm1, knots[k], lk + k, T::W, d, wa + k, &sin_el);
+      y[lane * T::WP + k] = loading_pW<R>(P, band, mu, z, sin_el);
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 2: m_k = M_k h^2 / 6 with m_{k-1} + 4 m_k + m_{k+1} = y_{k-1} - 2 y_k + y_{k+1} ----
+  // not-a-knot (scipy interp1d kind="cubic", sim/atmosphere.py:73-80): m_1 = q_1 / 6, m_0 = 2 m_1 - m_2 (same at the end)
+  if (warp == 0 && lane < nd) {
+    R* yy = y + lane * T::WP;
+    R* mm = m + lane * T::WP;
+    const int lo = 1, hi = Wn - 2;  // local indices with Dirichlet values (exact at a true end, r/6 guess otherwise)
+    auto q = [&](int k) { return yy[k - 1] - (R)2 * yy[k] + yy[k + 1]; };
+    const R m_lo = q(lo) / (R)6, m_hi = q(hi) / (R)6;
+    mm[lo] = m_lo;
+    mm[hi] = m_hi;
+    if (hi - lo >= 2) {
+      R dprev = (R)0;
+      for (int k = lo + 1; k <= hi - 1; k++) {
+        R rhs = q(k);
+        if (k == lo + 1) rhs -= m_lo;
+        if (k == hi - 1) rhs -= m_hi;
+        dprev = (rhs - dprev) * cprime[k - lo - 1];
+        mm[k] = dprev;
+      }
+      for (int k = hi - 2; k >= lo + 1; k--) mm[k] -= cprime[k - lo - 1] * mm[k + 1];
+    }
+    mm[0] = (R)2 * mm[1] - mm[2];
+    mm[Wn - 1] = (R)2 * mm[Wn - 2] - mm[Wn - 3];
+  }
+  __syncthreads();
+
+  // ---- phase 3 ----
+  const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
+  for (int64_t j = j0 + threadIdx.x; j < j1; j += SY_THREADS) {
+    const double sfull = (P.t_full[j] - P.t_atm0) / P.timestep;
+    int i = (int)floor(sfull);
+    i = min(max(i, 0), n - 2);
+    const R s = (R)(sfull - (double)i);
+    const int li = i - wa;
+    const R a0 = (R)1 - s, a1 = s;
+    const R a2 = a0 * a0 * a0 - a0, a3 = s * s * s - s;
+    R cef = (R)0, sef = (R)0;
+    if (units == MATM_UNITS_KRJ) {
+      cef = (R)P.bore_full[2 * j];
+      sef = (R)P.bore_full[2 * j + 1];
+    }
+    for (int dd = 0; dd < nd; dd++) {
+      const R* yy = y + dd * T::WP + li;
+      const R* mm = m + dd * T::WP + li;
+      R val = a0 * yy[0] + a1 * yy[1] + a2 * mm[0] + a3 * mm[1];
+      val *= dc_gain[dd];
+      if (units == MATM_UNITS_KRJ) {
+        const R sin_el = dc_u[dd] * sef + dc_w[dd] * cef;  // Im q of the rolled offsets at the full rate
+        val = val / cal_denominator<R>(P, dc_band[dd], sin_el);
+      }
+      out[(dbase + dd) * P.n_t + j] = val;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// a14 alone (TOD.to): pW <-> K_RJ on an existing (n_det, n_t) array
+// ---------------------------------------------------------------------------------------------------------
+template <typename R>
+__global__ void __launch_bounds__(256) calibrate_kernel(const __grid_constant__ SynthParams P, int64_t det0,
+                                                        int64_t n_det, const R* __restrict__ in, R* __restrict__ out,
+                                                        int to_units) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= P.n_t) return;
+  const R cef = (R)P.bore_full[2 * j], sef = (R)P.bore_full[2 * j + 1];
+  for (int64_t d = blockIdx.y; d < n_det; d += gridDim.y) {
+    const int64_t dg = det0 + d;
+    const R sin_el = (R)P.det_full[2 * dg] * sef + (R)P.det_full[2 * dg + 1] * cef;
+    const R den = cal_denominator<R>(P, P.band_index[dg], sin_el);
+    const R x = in[d * P.n_t + j];
+    out[d * P.n_t + j] = to_units == MATM_UNITS_KRJ ? x / den : x * den;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// entry points
+// ---------------------------------------------------------------------------------------------------------
+static int check_ready(matm_handle* h, bool need_bands, int64_t det0, int64_t n_det) {
+  if (!h->have_scan || !h->have_layers || !h->have_dets || (need_bands && !h->have_bands))
+    MATM_FAIL_ARG(h, "Atmosphere must be initialized with a simulation (scan, layers, detectors, bands not all set)");
+  if (det0 < 0 || n_det < 1 || det0 + n_det > h->P.n_det) MATM_FAIL_ARG(h, "detector range out of bounds");
+  return MATM_OK;
+}
+
+extern "C" int matm_zenith_pwv(matm_handle* h, int64_t det0, int64_t n_det, double* out_dev, void* stream) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  int rc = check_ready(h, false, det0, n_det);
+  if (rc) return rc;
+  if (!out_dev) MATM_FAIL_ARG(h, "matm_zenith_pwv: null output");
+  const SynthParams& P = h->P;
+  const int n_ttiles = (P.n_t_atm + 127) / 128;
+  const int64_t blocks = ((n_det + DT - 1) / DT) * n_ttiles;
+  if (blocks > INT32_MAX) MATM_FAIL_ARG(h, "matm_zenith_pwv: too many tiles; split the detector range");
+  if (h->dtype == MATM_F64) {
+    size_t smem = (size_t)P.n_layers * 128 * sizeof(LayerKnot<double>);
+    MATM_CUDA(h, cudaFuncSetAttribute(zenith_pwv_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    zenith_pwv_kernel<double><<<(unsigned)blocks, SY_THREADS, smem, (cudaStream_t)stream>>>(P, det0, n_det, out_dev);
+  } else {
+    size_t smem = (size_t)P.n_layers * 128 * sizeof(LayerKnot<float>);
+    MATM_CUDA(h, cudaFuncSetAttribute(zenith_pwv_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    zenith_pwv_kernel<float><<<(unsigned)blocks, SY_THREADS, smem, (cudaStream_t)stream>>>(P, det0, n_det, out_dev);
+  }
+  MATM_LAUNCHED(h);
+  return MATM_OK;
+}
+
+extern "C" int matm_upsample_linear(matm_handle* h, const double* in_dev, int64_t n_det, double* out_dev, void* stream) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (!h->have_scan) MATM_FAIL_ARG(h, "matm_upsample_linear: call matm_set_scan first");
+  if (!in_dev || !out_dev || n_det < 1) MATM_FAIL_ARG(h, "matm_upsample_linear: bad arguments");
+  dim3 grid((unsigned)((h->P.n_t + 255) / 256), (unsigned)min((int64_t)1024, n_det));
+  upsample_linear_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(h->P, in_dev, n_det, out_dev);
+  MATM_LAUNCHED(h);
+  return MATM_OK;
+}
+
+template <typename R>
+static size_t synth_smem(int n_layers) {
+  using T = Tile<R>;
+  return (size_t)2 * DT * T::WP * sizeof(R) + T::W * sizeof(R) + T::W * sizeof(Knot<R>) +
+         (size_t)n_layers * T::W * sizeof(LayerKnot<R>);
+}
+
+static int launch_synth(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, int units, int apply_gain,
+                        cudaStream_t st) {
+  const SynthParams& P = h->P;
+  if (P.n_t_atm < 4) MATM_FAIL_ARG(h, "cubic upsample needs at least 4 atmosphere-rate samples (scipy interp1d kind='cubic')");
+  if (h->dtype == MATM_F64) {
+    const int n_ttiles = (P.n_t_atm - 1 + Tile<double>::KT - 1) / Tile<double>::KT;
+    const int64_t blocks = ((n_det + DT - 1) / DT) * n_ttiles;
+    if (blocks > INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize: too many tiles; split the detector range");
+    size_t smem = synth_smem<double>(P.n_layers);
+    MATM_CUDA(h, cudaFuncSetAttribute(synth_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    synth_kernel<double><<<(unsigned)blocks, SY_THREADS, smem, st>>>(P, det0, n_det, (double*)out_dev, units, apply_gain);
+  } else {
+    const int n_ttiles = (P.n_t_atm - 1 + Tile<float>::KT - 1) / Tile<float>::KT;
+    const int64_t blocks = ((n_det + DT - 1) / DT) * n_ttiles;
+    if (blocks > INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize: too many tiles; split the detector range");
+    size_t smem = synth_smem<float>(P.n_layers);
+    MATM_CUDA(h, cudaFuncSetAttribute(synth_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    synth_kernel<float><<<(unsigned)blocks, SY_THREADS, smem, st>>>(P, det0, n_det, (float*)out_dev, units, apply_gain);
+  }
+  MATM_LAUNCHED(h);
+  return MATM_OK;
+}
+
+extern "C" int matm_synthesize(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, int units, int apply_gain,
+                               void* stream) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  int rc = check_ready(h, true, det0, n_det);
+  if (rc) return rc;
+  if (!out_dev || (units != MATM_UNITS_PW && units != MATM_UNITS_KRJ)) MATM_FAIL_ARG(h, "matm_synthesize: bad arguments");
+  return launch_synth(h, det0, n_det, out_dev, units, apply_gain, (cudaStream_t)stream);
+}
+
+extern "C" int matm_calibrate(matm_handle* h, int64_t det0, int64_t n_det, const void* in_dev, void* out_dev, int to_units,
+                              void* stream) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (!h->have_scan || !h->have_dets || !h->have_bands) MATM_FAIL_ARG(h, "matm_calibrate: scan, detectors and bands must be set");
+  if (det0 < 0 || n_det < 1 || det0 + n_det > h->P.n_det || !in_dev || !out_dev ||
+      (to_units != MATM_UNITS_PW && to_units != MATM_UNITS_KRJ))
+    MATM_FAIL_ARG(h, "matm_calibrate: bad arguments");
+  dim3 grid((unsigned)((h->P.n_t + 255) / 256), (unsigned)min((int64_t)2048, n_det));
+  if (h->dtype == MATM_F64)
+    calibrate_kernel<double><<<grid, 256, 0, (cudaStream_t)stream>>>(h->P, det0, n_det, (const double*)in_dev, (double*)out_dev, to_units);
+  else
+    calibrate_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(h->P, det0, n_det, (const float*)in_dev, (float*)out_dev, to_units);
+  MATM_LAUNCHED(h);
+  return MATM_OK;
+}
+
+// End-to-end delivery into host memory: detector chunks, two staging buffers, copy of chunk c overlapped with
+// the kernel of chunk c + 1.
+extern "C" int matm_synthesize_host(matm_handle* h, int64_t det0, int64_t n_det, void* out_host, int units, int apply_gain) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  int rc = check_ready(h, true, det0, n_det);
+  if (rc) return rc;
+  if (!out_host) MATM_FAIL_ARG(h, "matm_synthesize_host: null output");
+  const size_t esz = h->dtype == MATM_F64 ? 8 : 4;
+  const size_t row = (size_t)h->P.n_t * esz;
+  // chunk: a multiple of DT detectors, about 256 MiB
+  int64_t chunk = (int64_t)(((size_t)256 << 20) / row);
+  chunk = (chunk / DT) * DT;
+  if (chunk < DT) chunk = DT;
+  if (chunk > n_det) chunk = n_det;
+  const size_t need = (size_t)chunk * row;
+  if (h->stage_bytes < need) {
+    for (int i = 0; i < 2; i++) {
+      if (h->stage_dev[i]) MATM_CUDA(h, cudaFree(h->stage_dev[i]));
+      h->stage_dev[i] = nullptr;
+      MATM_CUDA(h, cudaMalloc(&h->stage_dev[i], need));
+      if (!h->stage_stream[i]) MATM_CUDA(h, cudaStreamCreateWithFlags(&h->stage_stream[i], cudaStreamNonBlocking));
+    }
+    h->stage_bytes = need;
+  }
+  int c = 0;
+  for (int64_t d = 0; d < n_det; d += chunk, c++) {
+    const int b = c & 1;
+    const int64_t nd = (n_det - d < chunk) ? (n_det - d) : chunk;
+    cudaStream_t st = h->stage_stream[b];  // stream order protects the staging buffer from reuse before its copy ends
+    rc = launch_synth(h, det0 + d, nd, h->stage_dev[b], units, apply_gain, st);
+    if (rc) return rc;
+    MATM_CUDA(h, cudaMemcpyAsync((char*)out_host + (size_t)d * row, h->stage_dev[b], (size_t)nd * row, cudaMemcpyDeviceToHost, st));
+  }
+  MATM_CUDA(h, cudaStreamSynchronize(h->stage_stream[0]));
+  MATM_CUDA(h, cudaStreamSynchronize(h->stage_stream[1]));
+  return MATM_OK;
+}

@@ -1,0 +1,135 @@
+"""``Simulation(instrument, plans, site, atmosphere="2d").run()`` for the atmosphere field, with maria's interface
+(maria/sim/simulation.py:76-272, maria/sim/observation.py:27-102, maria/sim/atmosphere.py:23-84).
+
+``run()`` goes through ONE fused kernel per observation (line-of-sight sampling of all layers, emission lookup, cubic
+upsample, gain, pW -> K_RJ); the mixin methods ``_simulate_atmosphere`` / ``_compute_atmospheric_loading`` keep the
+reference's staged interface for callers that want the intermediates.
+"""
+from __future__ import annotations
+
+import logging
+import time as ttime
+
+import numpy as np
+
+from . import _lib, host
+from .atmosphere import Atmosphere, Boresight, LazyCoords
+from .tod import TOD
+
+logger = logging.getLogger("maria_b200")
+
+
+class LazyArray:
+    """A (n_det, n_t) array that is evaluated on the device when converted (``np.asarray``) or sliced."""
+
+    def __init__(self, shape, dtype, compute):
+        self.shape, self.dtype, self._compute = tuple(shape), np.dtype(dtype), compute
+
+    def compute_device(self):
+        return self._compute()
+
+    def __array__(self, dtype=None, copy=None):
+        a = self._compute().cpu().numpy()
+        return a.astype(dtype) if dtype is not None else a
+
+    def __getitem__(self, key):
+        return np.asarray(self)[key]
+
+
+class Observation:
+    """The fields of maria/sim/observation.py:27-102 that the atmosphere path reads."""
+
+    def __init__(self, instrument, plan, site, atmosphere=None, atmosphere_kwargs=None):
+        self.instrument, self.plan, self.site = instrument, plan, site
+        self.boresight = Boresight(plan.time, plan.phi, plan.theta)  # :46-52
+        dets = instrument.dets
+        self.offsets = dets.offsets @ host.rotation_matrix_2d(np.radians(getattr(plan, "roll", 0.0))).T  # :55-58
+        self.coords = LazyCoords(self.boresight.t, self.boresight.az, self.boresight.el, self.offsets)
+        min_el = np.degrees(self.boresight.el.min())
+        if min_el < 5:  # :67-71 (PointingError in the reference)
+            raise ValueError(f"Minimum elevation is {min_el:.2f} degrees; the atmosphere model needs at least 5 degrees.")
+        self.loading = {}
+        self.atmosphere = None
+        if atmosphere:  # :88-96
+            kw = dict(atmosphere_kwargs or {})
+            kw.setdefault("region", site.region)
+            kw.setdefault("altitude", site.altitude)
+            kw.setdefault("timestamp", float(np.mean(plan.time)))
+            self.atmosphere = Atmosphere(model=atmosphere, **kw)
+
+
+class AtmosphereMixin:
+    """maria/sim/atmosphere.py:23-84."""
+
+    def _simulate_atmosphere(self, obs):
+        atm = obs.atmosphere
+        atm.simulate_pwv(obs.instrument)
+        ctx = atm.ctx
+        n_det, n_t = obs.instrument.dets.n, len(obs.boresight.t)
+
+        def upsampled():  # linear interp1d to the full rate (:30-37)
+            zp = atm.zenith_pwv_device()
+            out = ctx.empty((n_det, n_t), ctx.torch.float64)
+            ctx.check(ctx.lib.matm_upsample_linear(ctx.h, zp.data_ptr(), n_det, out.data_ptr(), ctx.stream_ptr()))
+            return out
+
+        obs.zenith_scaled_pwv = LazyArray((n_det, n_t), np.float64, upsampled)
+
+    def _compute_atmospheric_loading(self, obs, det0=0, n_det=None, units="pW", apply_gain=False):
+        """(n_det, n_t) loading [pW] in ``self.dtype`` on the device (:39-84): emission lookup x Mueller[0, 0] at the
+        atmosphere rate, cubic (not-a-knot) upsample to the full rate."""
+        atm = obs.atmosphere
+        ctx = atm.ctx
+        n_det = obs.instrument.dets.n - det0 if n_det is None else n_det
+        out = ctx.empty((n_det, len(obs.boresight.t)))
+        ctx.check(ctx.lib.matm_synthesize(ctx.h, det0, n_det, out.data_ptr(), _lib.UNITS_KRJ if units == "K_RJ" else _lib.UNITS_PW,
+                                          1 if apply_gain else 0, ctx.stream_ptr()))
+        return out
+
+
+class Simulation(AtmosphereMixin):
+    """maria/sim/simulation.py:76-272, restricted to the atmosphere field.
+
+    ``dtype`` is the TOD dtype as in the reference (float32 default; float64 selects the fp64 validation arithmetic).
+    ``det_range=(first, count)`` restricts synthesis to a contiguous detector shard (multi-GPU, one process per GPU).
+    """
+
+    def __init__(self, instrument, plans, site, atmosphere=None, atmosphere_kwargs=None, dtype=np.float32, noise=False,
+                 progress_bars=False, det_range=None, **kwargs):
+        self.instrument, self.site = instrument, site
+        self.plans = plans if isinstance(plans, (list, tuple)) else [plans]
+        self.dtype = np.dtype(dtype)
+        self.det_range = det_range
+        self.disable_progress_bars = not progress_bars
+        akw = dict(atmosphere_kwargs or {})
+        akw.setdefault("precision", "fp64" if self.dtype == np.float64 else "fp32")
+        self.obs_list = []
+        for plan in self.plans:  # :142-157
+            obs = Observation(instrument, plan, site, atmosphere=atmosphere, atmosphere_kwargs=akw)
+            if obs.atmosphere is not None:
+                t0 = ttime.monotonic()
+                obs.atmosphere.initialize(obs)
+                logger.debug(f"Initialized atmosphere in {ttime.monotonic() - t0:.2f} s")
+            self.obs_list.append(obs)
+
+    def run(self, units="K_RJ"):
+        """:201-211 -- one TOD per plan, in ``units``."""
+        return [self.run_obs(obs, units=units) for obs in self.obs_list]
+
+    def run_obs(self, obs, units="pW"):
+        """:213-272, atmosphere branch; the reference builds the pW TOD and converts, here both happen in the kernel."""
+        atm = obs.atmosphere
+        if atm is None:
+            raise RuntimeError("this build synthesises the atmosphere field only: pass atmosphere='2d'")
+        dets = obs.instrument.dets
+        self._simulate_atmosphere(obs)  # :216-221 (generates the layers)
+        gain_error = np.exp(dets.gain_error * atm.rng.standard_normal(size=dets.n))  # :239-241
+        atm.set_gain(gain_error)
+        det0, n_det = self.det_range if self.det_range is not None else (0, dets.n)
+        data = self._compute_atmospheric_loading(obs, det0, n_det, units=units, apply_gain=True)
+        obs.loading["atmosphere"] = data
+        atm.check_flags()
+        metadata = {"atmosphere": True, "sim_time": ttime.time(), "altitude": float(obs.site.altitude),
+                    "region": obs.site.region, "pwv": atm.cal_pwv, "base_temperature": atm.cal_T0, "det0": det0}  # :249-263
+        return TOD(data={"atmosphere": data}, dets=dets, coords=obs.coords, units=units, dtype=self.dtype,
+                   metadata=metadata, calibrator=atm)

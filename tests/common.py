@@ -1,0 +1,50 @@
+"""Shared helpers of the test-suite: rebuild the inputs of a golden fixture, run the oracle, compare."""
+import os
+
+import numpy as np
+
+from maria_b200 import inputs as I
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load_case(name):
+    """Inputs of tests/golden/ref_<name>.npz (written by oracle/pin_against_reference.py) as duck-typed objects."""
+    fx = np.load(os.path.join(GOLDEN, f"ref_{name}.npz"), allow_pickle=False)
+    bands = []
+    for i, bname in enumerate(fx["band_names"]):
+        b = I.Band(str(bname), nu=fx[f"band{i}_nu"], tau=fx[f"band{i}_tau"], efficiency=float(fx["band_efficiency"][i]),
+                   gain_error=float(fx["band_gain_error"][i]))
+        b.efficiency = float(fx["band_efficiency"][i])  # Band(nu=, tau=) rescales; keep the reference's values
+        b.tau = np.array(fx[f"band{i}_tau"])
+        bands.append(b)
+    arr = I.Array(fx["xi"], fx["eta"], fx["band_name"].astype(str), bands, fx["gamma"], fx["primary_size"])
+    arr.band_center = np.array(fx["band_center"])
+    for b in bands:
+        b.center = float(arr.band_center[arr.band_name == b.name][0])
+    inst = I.Instrument(arr, name=str(fx["instrument"]))
+    site = I.Site(str(fx["site_region"]), float(fx["site_altitude"]))
+    plan = I.Plan(fx["time"], fx["az"], fx["el"])
+    profiles = {f: np.array(fx[f"weather_{f}"]) for f in I.Weather.fields}
+    weather = I.Weather(site.region, site.altitude, profiles, wind_corrected=True)
+    spectrum = I.make_spectrum(region=site.region)
+    return dict(fx=fx, instrument=inst, site=site, plan=plan, weather=weather, spectrum=spectrum, seed=int(fx["seed"]))
+
+
+def relmax(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / np.max(np.abs(b)))
+
+
+def small_case(n_det=64, duration=20.0, sample_rate=20.0, pattern="daisy", seed=7, bands=None, polarized=False,
+               fov_deg=0.5, primary=6.0, pwv=1.0, altitude=5190.0, scan_options=None, center=(60.0, 50.0)):
+    """A synthetic configuration small enough for the oracle to finish in seconds."""
+    bands = bands or [I.Band("f090", center=90e9, width=20e9, gain_error=5e-2),
+                      I.Band("f150", center=150e9, width=30e9, gain_error=5e-2)]
+    inst = I.make_instrument(n_det // (len(bands) * (2 if polarized else 1)), bands, fov_deg, primary, polarized=polarized)
+    site = I.Site("synthetic", altitude)
+    plan = I.Plan.generate(duration=duration, sample_rate=sample_rate, scan_center=center, scan_pattern=pattern,
+                           scan_options=scan_options or dict(radius_deg=0.5, speed_deg=0.5))
+    weather = I.make_weather("synthetic", altitude, pwv=pwv)
+    spectrum = I.make_spectrum("synthetic")
+    return dict(instrument=inst, site=site, plan=plan, weather=weather, spectrum=spectrum, seed=seed)

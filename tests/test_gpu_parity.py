@@ -1,0 +1,143 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the reference's own outputs (tests/golden, written by
+oracle/pin_against_reference.py from the unmodified reference) and against the oracle on fresh seeded inputs.
+
+Tolerances (stated here, used below):
+  fp64 path vs reference / oracle, identical host noise ........ 1e-10 relative (max |diff| / max |ref|)
+  fp32 path vs the float64 oracle ............................... 2e-6 relative on the total TOD,
+                                                                  2e-4 relative on its fluctuating part
+"""
+import numpy as np
+import pytest
+
+import maria_b200 as M
+from common import load_case, relmax, small_case
+from oracle import atm_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+TOL64 = 1e-10
+TOL32_TOTAL = 2e-6
+TOL32_FLUCT = 2e-4
+
+
+def run_device(case, dtype, units="K_RJ", **akw):
+    np.random.seed(case["seed"])
+    sim = M.Simulation(case["instrument"], case["plan"], case["site"], atmosphere="2d", dtype=dtype,
+                       atmosphere_kwargs=dict(weather=case["weather"], spectrum=case["spectrum"], geometry="exact", **akw))
+    tod = sim.run(units=units)[0]
+    return sim, tod
+
+
+def run_oracle(case):
+    np.random.seed(case["seed"])
+    rec = {}
+    res = O.simulate(case["instrument"], case["plan"], case["site"], case["weather"], case["spectrum"], np.random,
+                     dtype=np.float64, record=rec)
+    res["record"] = rec
+    return res
+
+
+@pytest.mark.parametrize("name", ["m2_daisy", "1deg_ces"])
+def test_fp64_matches_reference_golden(cuda, name):
+    case = load_case(name)
+    fx = case["fx"]
+    sim, tod = run_device(case, np.float64)
+    atm = sim.obs_list[0].atmosphere
+    for k, p in atm.processes.items():  # a5: the generated layers
+        assert relmax(p.values, fx[f"ref_values_{k}"]) < TOL64, k
+    assert relmax(atm.zenith_scaled_pwv, fx["ref_zenith_scaled_pwv"]) < TOL64  # a6 + a7 + a8 + a9
+    sel = fx["det_sel"]
+    krj = tod.data["atmosphere"]
+    assert krj.dtype == np.float64 and krj.shape == (len(fx["xi"]), len(fx["time"]))
+    assert relmax(krj[sel], fx["ref_tod_K_RJ_sel"]) < TOL64  # a10..a14
+    pw = tod.to("pW").data["atmosphere"]
+    assert relmax(pw[sel], fx["ref_loading_pW_sel"]) < TOL64
+    back = tod.to("pW").to("K_RJ").data["atmosphere"]  # reference: tests/tod/test_tod.py:37-49 round trip
+    assert relmax(back, krj) < 1e-14
+
+
+@pytest.mark.parametrize("name", ["m2_daisy", "1deg_ces"])
+def test_fp32_within_stated_bound_of_reference(cuda, name):
+    case = load_case(name)
+    fx = case["fx"]
+    sim, tod = run_device(case, np.float32)
+    krj = tod.data["atmosphere"]
+    assert krj.dtype == np.float32
+    sel = fx["det_sel"]
+    ref = fx["ref_tod_K_RJ_sel"]
+    assert relmax(krj[sel], ref) < TOL32_TOTAL
+    fl_ref = ref - ref.mean(axis=1, keepdims=True)
+    fl_dev = krj[sel].astype(np.float64) - ref.mean(axis=1, keepdims=True)
+    assert np.max(np.abs(fl_dev - fl_ref)) / np.max(np.abs(fl_ref)) < TOL32_FLUCT
+
+
+def test_stages_against_oracle_fresh_inputs(cuda):
+    """Synthetic 2-band polarised array, back-and-forth scan: every stage against the oracle with the same noise."""
+    case = small_case(n_det=96, duration=30.0, sample_rate=25.0, pattern="back_and_forth", polarized=True, seed=11)
+    res = run_oracle(case)
+    sim, tod = run_device(case, np.float64)
+    obs, atm = sim.obs_list[0], sim.obs_list[0].atmosphere
+    o_atm = res["atmosphere"]
+    for k, p in atm.processes.items():
+        assert relmax(p.values, o_atm.processes[k].values) < TOL64
+    for li, sm in res["record"]["smoothed"].items():  # a8
+        assert relmax(atm.smoothed_layer(li), sm) < TOL64
+    assert relmax(atm.zenith_scaled_pwv, o_atm.zenith_scaled_pwv) < TOL64
+    assert relmax(np.asarray(obs.zenith_scaled_pwv), res["obs"].zenith_scaled_pwv) < TOL64  # a10
+    loading = sim._compute_atmospheric_loading(obs).cpu().numpy()  # a11 + a12, no gain
+    o_loading = res["loading_pW"] / res["record"]["gain_error"][:, None]
+    assert relmax(loading, o_loading) < TOL64
+    assert relmax(tod.data["atmosphere"], res["tod_K_RJ"]) < TOL64
+
+
+def test_detector_shards_tile_the_full_tod(cuda):
+    """Detector sharding (multi-GPU partitioning) is exact: shards computed separately equal the full run, bit for bit."""
+    case = small_case(n_det=80, duration=12.0, sample_rate=20.0, seed=5)
+    sim, tod = run_device(case, np.float32)
+    full = tod.data["atmosphere"]
+    obs = sim.obs_list[0]
+    parts = [sim._compute_atmospheric_loading(obs, d0, n, units="K_RJ", apply_gain=True).cpu().numpy()
+             for d0, n in [(0, 33), (33, 7), (40, 40)]]
+    assert np.array_equal(np.concatenate(parts, axis=0), full)
+
+
+def test_philox_layers_have_matern_statistics(cuda):
+    """Production RNG: unit marginal variance and the Matern structure function across the extrusion axis."""
+    case = small_case(n_det=32, duration=60.0, sample_rate=10.0, seed=3)
+    np.random.seed(3)
+    sim = M.Simulation(case["instrument"], case["plan"], case["site"], atmosphere="2d",
+                       atmosphere_kwargs=dict(weather=case["weather"], spectrum=case["spectrum"], noise="philox", seed=99))
+    atm = sim.obs_list[0].atmosphere
+    k = max(atm.processes)
+    p = atm.processes[k]
+    var, sf = [], []
+    lags = np.array([1, 2, 4, 8])
+    for seed in range(24):
+        atm.seed = 1000 + seed
+        atm.generate()
+        v = p.values
+        var.append(v.var())
+        sf.append([np.mean((v[l:] - v[:-l]) ** 2) for l in lags])
+    cov = p.callback(lags * p.extrusion_res)
+    expected_sf = 2 * (1 - cov)
+    assert abs(np.mean(var) - 1) < 0.15
+    assert np.all(np.abs(np.mean(sf, axis=0) / expected_sf - 1) < 0.2)
+    # two different subsequences / seeds are different, the same seed reproduces
+    atm.seed = 5
+    atm.generate()
+    a = p.values.copy()
+    atm.generate()
+    assert np.array_equal(a, p.values)
+
+
+def test_out_of_grid_raises_like_the_reference(cuda):
+    """A line of sight outside a layer must raise (atmosphere.py:368-369), not clamp."""
+    case = small_case(n_det=16, duration=10.0, sample_rate=10.0, seed=2)
+    sim, _ = run_device(case, np.float32)
+    atm = sim.obs_list[0].atmosphere
+    for p in atm.processes.values():
+        p.vx = p.vx + 500.0  # blow the footprint out of the generated grids
+    atm._layers_set = False
+    atm.generate()
+    with pytest.raises(RuntimeError, match="introduced nans"):
+        atm.zenith_scaled_pwv
