@@ -53,14 +53,53 @@ __global__ void jstart_kernel(const double* __restrict__ t, int64_t n_t, double 
   jstart[k] = lo;
 }
 
-extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, double t_atm0, double timestep, const double* az_atm_host,
-                             const double* el_atm_host, int64_t n_t, const double* t_host, const double* az_host,
-                             const double* el_host) {
+// Not-a-knot cubic spline through the knots x_k (scipy interp1d kind="cubic" = make_interp_spline k=3, default
+// boundary condition; sim/atmosphere.py:73-80), as the tridiagonal system for the second derivatives M_k in units of
+// `timestep`: rows k = 1 .. n-2,  a_k M_{k-1} + b_k M_k + c_k M_{k+1} = 6 [(y_{k+1}-y_k)/h_k - (y_k-y_{k-1})/h_{k-1}],
+// with M_0 and M_{n-1} eliminated through the continuity of the third derivative at x_1 and x_{n-2}.  The forward
+// elimination factors depend on the knots only and are computed once, here (one thread, n steps).
+__global__ void spline_coef_kernel(const double* __restrict__ x, int n, double timestep, double* __restrict__ spl) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  for (int k = 0; k < n - 1; k++) {
+    double hk = (x[k + 1] - x[k]) / timestep;
+    spl[5 * k + 0] = 1.0 / hk;
+    spl[5 * k + 1] = hk * hk / 6.0;
+  }
+  spl[5 * (n - 1) + 0] = spl[5 * (n - 1) + 1] = 0.0;
+  for (int j = 2; j < 5; j++) spl[j] = spl[5 * (n - 1) + j] = 0.0;
+  double cp_prev = 0.0;
+  for (int k = 1; k <= n - 2; k++) {
+    double h0 = (x[k] - x[k - 1]) / timestep, h1 = (x[k + 1] - x[k]) / timestep;
+    double a = h0, b = 2.0 * (h0 + h1), c = h1;
+    if (k == 1) {  // M_0 = M_1 - (h_0 / h_1) (M_2 - M_1)
+      a = 0.0;
+      b = 3.0 * h0 + 2.0 * h1 + h0 * h0 / h1;
+      c = h1 - h0 * h0 / h1;
+    }
+    if (k == n - 2) {  // M_{n-1} = M_{n-2} + (h_{n-2} / h_{n-3}) (M_{n-2} - M_{n-3});  n >= 4, so k > 1 here
+      a = h0 - h1 * h1 / h0;
+      b = 2.0 * h0 + 3.0 * h1 + h1 * h1 / h0;
+      c = 0.0;
+    }
+    double w = 1.0 / (b - a * cp_prev);
+    cp_prev = c * w;
+    spl[5 * k + 2] = w;
+    spl[5 * k + 3] = a * w;
+    spl[5 * k + 4] = cp_prev;
+  }
+}
+
+extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_host, double timestep,
+                             const double* az_atm_host, const double* el_atm_host, int64_t n_t, const double* t_host,
+                             const double* az_host, const double* el_host) {
   MATM_CHECK_HANDLE(h);
   if (matm_set_device(h)) return MATM_ERR_CUDA;
   if (n_t_atm < 2 || n_t < 1 || !(timestep > 0)) MATM_FAIL_ARG(h, "matm_set_scan: need n_t_atm >= 2, n_t >= 1, timestep > 0");
-  if (!az_atm_host || !el_atm_host || !t_host || !el_host) MATM_FAIL_ARG(h, "matm_set_scan: null pointer");
+  if (!t_atm_host || !az_atm_host || !el_atm_host || !t_host || !el_host) MATM_FAIL_ARG(h, "matm_set_scan: null pointer");
+  for (int k = 1; k < n_t_atm; k++)
+    if (!(t_atm_host[k] > t_atm_host[k - 1])) MATM_FAIL_ARG(h, "matm_set_scan: knot times must increase");
   (void)az_host;  // the full-rate azimuth does not enter the path (only the elevation does, tod.py:126-133)
+  const double t_atm0 = t_atm_host[0];
   double *az_d = nullptr, *el_d = nullptr, *elf_d = nullptr;
   int rc;
   if ((rc = matm_upload(h, &az_d, az_atm_host, (size_t)n_t_atm))) return rc;
@@ -70,12 +109,18 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, double t_atm0, double 
   if ((rc = matm_upload(h, &h->bore_full, (const double*)nullptr, (size_t)n_t * 2))) return rc;
   if ((rc = matm_upload(h, &h->t_full, t_host, (size_t)n_t))) return rc;
   if ((rc = matm_upload(h, &h->jstart, (const int64_t*)nullptr, (size_t)n_t_atm + 1))) return rc;
+  if ((rc = matm_upload(h, &h->t_atm, t_atm_host, (size_t)n_t_atm))) return rc;
+  if ((rc = matm_upload(h, &h->spl, (const double*)nullptr, (size_t)n_t_atm * 5))) return rc;
   bore_atm_kernel<<<(n_t_atm + 255) / 256, 256>>>(az_d, el_d, h->bore_atm, n_t_atm);
   MATM_LAUNCHED(h);
   bore_full_kernel<<<(unsigned)((n_t + 255) / 256), 256>>>(elf_d, h->bore_full, n_t);
   MATM_LAUNCHED(h);
   jstart_kernel<<<(n_t_atm + 1 + 255) / 256, 256>>>(h->t_full, n_t, t_atm0, timestep, n_t_atm, h->jstart);
   MATM_LAUNCHED(h);
+  if (n_t_atm >= 4) {
+    spline_coef_kernel<<<1, 32>>>(h->t_atm, n_t_atm, timestep, h->spl);
+    MATM_LAUNCHED(h);
+  }
   MATM_CUDA(h, cudaDeviceSynchronize());
   cudaFree(az_d);
   cudaFree(el_d);
@@ -89,6 +134,8 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, double t_atm0, double 
   P.bore_full = h->bore_full;
   P.t_full = h->t_full;
   P.jstart = h->jstart;
+  P.t_atm = h->t_atm;
+  P.spl = h->spl;
   h->have_scan = true;
   h->have_layers = false;  // layer bases depend on the scan
   return MATM_OK;

@@ -53,7 +53,10 @@ __global__ void __launch_bounds__(256) upsample_linear_kernel(const __grid_const
   const double t = P.t_full[j];
   int i = (int)floor((t - P.t_atm0) / P.timestep);
   i = min(max(i, 0), P.n_t_atm - 2);
-  const double x0 = P.t_atm0 + i * P.timestep, x1 = P.t_atm0 + (i + 1) * P.timestep;
+  // the interval in the actual (rounded) knot vector, as np.searchsorted(x, t) - 1 clipped to [0, n - 2]
+  while (i > 0 && !(P.t_atm[i] < t)) i--;
+  while (i < P.n_t_atm - 2 && P.t_atm[i + 1] < t) i++;
+  const double x0 = P.t_atm[i], x1 = P.t_atm[i + 1];
   const double s = (t - x0) / (x1 - x0);
   for (int64_t d = blockIdx.y; d < n_det; d += gridDim.y) {
     const double y0 = in[d * P.n_t_atm + i], y1 = in[d * P.n_t_atm + i + 1];
@@ -75,8 +78,8 @@ __global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant
   extern __shared__ __align__(16) unsigned char dyn[];
   R* y = reinterpret_cast<R*>(dyn);                       // [DT][WP]
   R* m = y + DT * T::WP;                                  // [DT][WP]
-  R* cprime = m + DT * T::WP;                             // [W] Thomas coefficients
-  Knot<R>* knots = reinterpret_cast<Knot<R>*>(cprime + T::W);
+  R* spl = m + DT * T::WP;                                // [W][5] spline system of the window (see SynthParams::spl)
+  Knot<R>* knots = reinterpret_cast<Knot<R>*>(spl + 5 * T::W);
   LayerKnot<R>* lk = reinterpret_cast<LayerKnot<R>*>(knots + T::W);  // [n_layers][W]
   __shared__ R dc_u[DT], dc_w[DT], dc_gain[DT];
   __shared__ int dc_band[DT];
@@ -104,15 +107,7 @@ __global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant
       dc_band[dd] = P.band_index[d];
     }
   }
-  if (threadIdx.x == 0) {
-    // forward-elimination coefficients of the (1, 4, 1) system: c'_1 = 1/4, c'_k = 1 / (4 - c'_{k-1})
-    R c = (R)0.25;
-    cprime[0] = c;
-    for (int k = 1; k < T::W; k++) {
-      c = (R)1 / ((R)4 - c);
-      cprime[k] = c;
-    }
-  }
+  for (int e = threadIdx.x; e < 5 * Wn; e += SY_THREADS) spl[e] = (R)P.spl[5 * (size_t)wa + e];
   __syncthreads();
 
   // ---- phase 1 ----
@@ -130,42 +125,42 @@ __global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant
   }
   __syncthreads();
 
-  // ---- phase 2: m_k = M_k h^2 / 6 with m_{k-1} + 4 m_k + m_{k+1} = y_{k-1} - 2 y_k + y_{k+1} ----
-  // not-a-knot (scipy interp1d kind="cubic", sim/atmosphere.py:73-80): m_1 = q_1 / 6, m_0 = 2 m_1 - m_2 (same at the end)
+  // ---- phase 2: second derivatives M_k of the not-a-knot cubic spline through the window's knots ----
+  // Rows glo..ghi of the global tridiagonal system, swept with the global elimination factors.  At a true end of the
+  // series the sweep starts / ends exactly; at an artificial end it starts from the locally-constant guess
+  // M = d / (a + b + c), whose error decays by ~(2 - sqrt 3) per knot across the halo.
   if (warp == 0 && lane < nd) {
     R* yy = y + lane * T::WP;
     R* mm = m + lane * T::WP;
-    const int lo = 1, hi = Wn - 2;  // local indices with Dirichlet values (exact at a true end, r/6 guess otherwise)
-    auto q = [&](int k) { return yy[k - 1] - (R)2 * yy[k] + yy[k + 1]; };
-    const R m_lo = q(lo) / (R)6, m_hi = q(hi) / (R)6;
-    mm[lo] = m_lo;
-    mm[hi] = m_hi;
-    if (hi - lo >= 2) {
-      R dprev = (R)0;
-      for (int k = lo + 1; k <= hi - 1; k++) {
-        R rhs = q(k);
-        if (k == lo + 1) rhs -= m_lo;
-        if (k == hi - 1) rhs -= m_hi;
-        dprev = (rhs - dprev) * cprime[k - lo - 1];
-        mm[k] = dprev;
-      }
-      for (int k = hi - 2; k >= lo + 1; k--) mm[k] -= cprime[k - lo - 1] * mm[k + 1];
+    const int lo = 1, hi = Wn - 2;  // local rows; global row = wa + local
+    auto invh = [&](int k) { return spl[5 * k + 0]; };
+    auto rhs = [&](int k) { return (R)6 * ((yy[k + 1] - yy[k]) * invh(k) - (yy[k] - yy[k - 1]) * invh(k - 1)); };
+    auto guess = [&](int k) { return rhs(k) / ((R)3 * ((R)1 / invh(k - 1) + (R)1 / invh(k))); };
+    R dp = (wa == 0) ? rhs(lo) * spl[5 * lo + 2] : guess(lo) * ((R)1 + spl[5 * lo + 4]);
+    mm[lo] = dp;
+    for (int k = lo + 1; k <= hi; k++) {
+      dp = rhs(k) * spl[5 * k + 2] - spl[5 * k + 3] * dp;
+      mm[k] = dp;
     }
-    mm[0] = (R)2 * mm[1] - mm[2];
-    mm[Wn - 1] = (R)2 * mm[Wn - 2] - mm[Wn - 3];
+    if (wb != n - 1) mm[hi] -= spl[5 * hi + 4] * guess(hi);
+    for (int k = hi - 1; k >= lo; k--) mm[k] -= spl[5 * k + 4] * mm[k + 1];
+    mm[0] = (wa == 0) ? mm[1] - (invh(1) / invh(0)) * (mm[2] - mm[1]) : mm[1];
+    mm[Wn - 1] = (wb == n - 1) ? mm[Wn - 2] + (invh(Wn - 3) / invh(Wn - 2)) * (mm[Wn - 2] - mm[Wn - 3]) : mm[Wn - 2];
   }
   __syncthreads();
 
   // ---- phase 3 ----
   const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
   for (int64_t j = j0 + threadIdx.x; j < j1; j += SY_THREADS) {
-    const double sfull = (P.t_full[j] - P.t_atm0) / P.timestep;
-    int i = (int)floor(sfull);
+    const double tj = P.t_full[j];
+    int i = (int)floor((tj - P.t_atm0) / P.timestep);  // the interval this tile was assigned (jstart uses the same rule)
     i = min(max(i, 0), n - 2);
-    const R s = (R)(sfull - (double)i);
+    const double xi = P.t_atm[i];
+    const R s = (R)((tj - xi) / (P.t_atm[i + 1] - xi));  // may leave [0, 1] by ~1e-6 (knot rounding) or at the ends
     const int li = i - wa;
     const R a0 = (R)1 - s, a1 = s;
-    const R a2 = a0 * a0 * a0 - a0, a3 = s * s * s - s;
+    const R h26 = spl[5 * li + 1];
+    const R a2 = h26 * (a0 * a0 * a0 - a0), a3 = h26 * (s * s * s - s);
     R cef = (R)0, sef = (R)0;
     if (units == MATM_UNITS_KRJ) {
       cef = (R)P.bore_full[2 * j];
@@ -251,7 +246,7 @@ extern "C" int matm_upsample_linear(matm_handle* h, const double* in_dev, int64_
 template <typename R>
 static size_t synth_smem(int n_layers) {
   using T = Tile<R>;
-  return (size_t)2 * DT * T::WP * sizeof(R) + T::W * sizeof(R) + T::W * sizeof(Knot<R>) +
+  return (size_t)2 * DT * T::WP * sizeof(R) + 5 * T::W * sizeof(R) + T::W * sizeof(Knot<R>) +
          (size_t)n_layers * T::W * sizeof(LayerKnot<R>);
 }
 
