@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""Benchmark of the atmospheric TOD synthesis path (BASELINE.json metric: detector-samples/s, % of HBM roofline).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one process per GPU under torchrun)
+  python bench.py --impl reference --steps K --warmup W    # the reference's CPU algorithm (oracle port) on host cores
+
+A step = one full pass of the hot path over one observation: Philox noise -> AR recurrence of all layers -> beam
+smoothing -> fused line-of-sight sampling / emission lookup / cubic upsample / gain / pW->K_RJ, producing the
+(n_det, n_t) float32 TOD.  Workload at N = 1: configs[3], the 100k-detector AtLAST-scale 1-hour raster the metric is
+quoted on (72 GB of TOD, fits one B200).  At N > 1 every rank synthesises its own 100k-detector shard of an
+N x 100k-detector focal plane (weak scaling, no data-path collective: the layers are regenerated from the same seed).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n-det", type=int, default=100_000, help="detectors per GPU")
+    ap.add_argument("--duration", type=float, default=3600.0)
+    ap.add_argument("--sample-rate", type=float, default=50.0)
+    ap.add_argument("--cpu-dets", type=int, default=64, help="detectors in the bounded CPU-baseline sample")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            self.path = tempfile.NamedTemporaryFile(delete=False, suffix=".csv").name
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", str(self.index)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return out
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def build_config(args, world):
+    from maria_b200 import configs
+
+    cfg = configs.c4_atlast(n_det=args.n_det, duration=args.duration, sample_rate=args.sample_rate, n_groups=world)
+    return cfg
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle (a port of the reference's numpy / scipy algorithm) on a bounded detector sample
+# ---------------------------------------------------------------------------------------------------------------
+def host_geometry(cfg, bind):
+    """Run this repo's host set-up (same layer table / stencil / A, B / transform the GPU arm uses)."""
+    import maria_b200 as M
+
+    np.random.seed(1234)
+    obs = M.Observation(cfg["instrument"], cfg["plan"], cfg["site"])
+    atm = M.Atmosphere(weather=cfg["weather"], spectrum=cfg["spectrum"], noise="philox", seed=1234, precision="fp32")
+    atm.initialize(obs, bind=bind)
+    return obs, atm
+
+
+def cpu_sample_runner(cfg, atm, n_sub):
+    """Returns (run, n_samples): ``run(seed)`` executes stages a5-a14 of the oracle for the first ``n_sub`` detectors
+    over the full scan (all layers at full size) and returns the K_RJ TOD."""
+    from maria_b200 import inputs as I
+    from oracle import atm_oracle as O
+
+    dets = cfg["instrument"].dets
+    sel = np.unique(np.linspace(0, dets.n - 1, min(n_sub, dets.n)).astype(int))  # spread over both bands
+    sub = I.Array(dets.xi[sel], dets.eta[sel], dets.band_name[sel], [b for b in dets.bands if b.name in set(dets.band_name[sel])],
+                  dets.gamma[sel], dets.primary_size[sel])
+    inst = I.Instrument(sub, name=cfg["instrument"].name)
+    geo = {k: dict(cross_section=p.cross_section, extrusion=p.extrusion, A=p.A, B=p.B, transform=p.transform, vx=p.vx, vy=p.vy,
+                   layer_index=p.layer_index, labels=p.labels, extrusion_res=p.extrusion_res) for k, p in atm.processes.items()}
+    o_obs = O.Observation(inst, cfg["plan"], cfg["site"])
+    o_atm = O.atmosphere_from_geometry(cfg["weather"], cfg["spectrum"], atm.layers, atm.timestep, atm.boresight.t,
+                                       atm.boresight.az, atm.boresight.el, sub.offsets, geo)
+
+    def run(seed):
+        rng = np.random.default_rng(seed)
+        loading, meta = O.run_obs(o_obs, o_atm, rng, dtype=np.float32)
+        return O.tod_to_K_RJ(loading, o_obs, o_atm, meta, out_dtype=np.float32)
+
+    return run, len(sel) * len(cfg["plan"].time)
+
+
+def time_cpu(run, n_samples, steps, warmup):
+    for w in range(warmup):
+        run(100 + w)
+    t0 = time.perf_counter()
+    for s in range(steps):
+        run(200 + s)
+    dt = (time.perf_counter() - t0) / steps
+    return n_samples / dt, dt
+
+
+def cpu_threads():
+    try:
+        from threadpoolctl import threadpool_info
+
+        return max([p.get("num_threads", 1) for p in threadpool_info()] + [1])
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg = build_config(args, 1)
+    _, atm = host_geometry(cfg, bind=False)
+    run, n_samples = cpu_sample_runner(cfg, atm, args.cpu_dets)
+    value, dt = time_cpu(run, n_samples, args.steps, min(args.warmup, 1))
+    sample = f"{args.cpu_dets} of {args.n_det} detectors (evenly spaced) x {len(cfg['plan'].time)} samples, all 8 layers at full size"
+    line = {
+        "impl": "reference", "metric": "atmospheric TOD detector-samples/sec", "value": value, "unit": "detector-samples/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args, cfg), "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "detector-samples/s", "cores": cpu_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "detector-samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(args, cfg):
+    return (f"C4 AtLAST-scale: {args.n_det} detectors/GPU, 2 bands, 8 turbulent layers, raster {args.duration:.0f} s at "
+            f"{args.sample_rate:.0f} Hz ({len(cfg['plan'].time)} samples/detector), units K_RJ")
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the CUDA arm
+# ---------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the CUDA path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    import maria_b200 as M
+
+    cfg = build_config(args, world)
+    np.random.seed(1234)  # identical host set-up on every rank
+    t0 = time.perf_counter()
+    sim = M.Simulation(cfg["instrument"], cfg["plan"], cfg["site"], atmosphere="2d", dtype=np.float32,
+                       det_range=(rank * args.n_det, args.n_det),
+                       atmosphere_kwargs=dict(weather=cfg["weather"], spectrum=cfg["spectrum"], noise="philox", seed=1234,
+                                              device=local))
+    setup_s = time.perf_counter() - t0
+    obs = sim.obs_list[0]
+    atm = obs.atmosphere
+    ctx = atm.ctx
+    dets = cfg["instrument"].dets
+    n_t = len(cfg["plan"].time)
+    det0, n_det = sim.det_range
+    gain = np.exp(dets.gain_error * np.random.standard_normal(size=dets.n))  # simulation.py:239-241
+    atm.set_gain(gain)
+    out = ctx.empty((n_det, n_t))  # the TOD shard, resident in HBM (72 GB at full size)
+
+    def step(i):
+        atm.seed = 1234 + i  # a fresh realisation every step: nothing can be cached
+        atm.generate()       # Philox -> B z GEMM -> AR chains (8 streams) -> beam smoothing
+        atm.synthesize(det0, n_det, units="K_RJ", apply_gain=True, out=out)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    atm.check_flags()
+    launches0 = ctx.launch_count
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    syn = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    ev[0].record()
+    for i in range(args.steps):
+        atm.seed = 5000 + i
+        atm.generate()
+        syn[i][0].record()
+        atm.synthesize(det0, n_det, units="K_RJ", apply_gain=True, out=out)
+        syn[i][1].record()
+    ev[1].record()
+    barrier()
+    clocks = sampler.stop()
+    launches = ctx.launch_count - launches0
+    total_ms = ev[0].elapsed_time(ev[1])
+    synth_ms = float(np.mean([a.elapsed_time(b) for a, b in syn]))
+    status = atm.check_flags()
+    if world > 1:
+        t = torch.tensor([total_ms, synth_ms], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, synth_ms = float(t[0]), float(t[1])
+    ms_per_step = total_ms / args.steps
+    value = world * n_det * n_t / (ms_per_step * 1e-3)
+
+    # ---- roofline of the dominant kernel (synth_kernel<float>) ----
+    layer_bytes = sum(4 * p.n_extrusion * p.n_cross_section for p in atm.processes.values())
+    n_atm = len(atm.boresight.t)
+    alg_bytes = 4 * n_det * n_t + layer_bytes + 16 * n_atm + 8 * n_t + 16 * n_det
+    peak, peak_src = measured_peak_gbs()
+    achieved = alg_bytes / (synth_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "synth_kernel<float>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "kernel_ms": synth_ms, "generate_ms": ms_per_step - synth_ms}
+
+    # ---- end to end through the public API with HOST buffers ----
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, torch, dist, world, local, sim, cfg, gain, out, barrier)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        del out
+        torch.cuda.empty_cache()
+        run, n_samples = cpu_sample_runner(cfg, atm, args.cpu_dets)
+        v, dt = time_cpu(run, n_samples, 1, 0)
+        cpu = {"value": v, "unit": "detector-samples/s", "cores": cpu_threads(), "kind": "port",
+               "sample": f"{args.cpu_dets} of {args.n_det} detectors (evenly spaced) x {n_t} samples, all layers at full size, "
+                         f"{dt:.1f} s of CPU work", "host_cpus": os.cpu_count()}
+    if rank == 0:
+        line = {
+            "metric": "atmospheric TOD detector-samples/sec", "value": value, "unit": "detector-samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args, cfg), "n_det_per_gpu": n_det, "n_t": n_t, "n_t_atm": n_atm,
+                       "layers": [[p.n_extrusion, p.n_cross_section] for p in atm.processes.values()],
+                       "l2": "output (n_det*n_t*4 B per step) is far larger than L2; layers are regenerated every step",
+                       "rng": "philox (device)", "setup_s": setup_s, "status": status},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, torch, dist, world, local, sim, cfg, gain, out_dev, barrier):
+    """The same step through the public API with host buffers: every step uploads the scan (boresight t/az/el), the
+    detector table and the gains from host memory, regenerates the layers and delivers the TOD shard into pinned host
+    memory (matm_synthesize_host: chunked, copies overlapped with the kernels)."""
+    obs = sim.obs_list[0]
+    atm = obs.atmosphere
+    det0, n_det = sim.det_range
+    n_t = len(cfg["plan"].time)
+    del out_dev
+    try:
+        host_out = torch.empty((n_det, n_t), dtype=torch.float32, pin_memory=True)
+        pinned = True
+    except Exception:
+        host_out = torch.empty((n_det, n_t), dtype=torch.float32)
+        pinned = False
+    dets = cfg["instrument"].dets
+    h2d = 8 * (3 * n_t + 3 * len(atm.boresight.t)) + dets.n * (16 + 16 + 4 + 8 + 8)
+    d2h = host_out.numel() * 4
+
+    def step(i):
+        atm.seed = 9000 + i
+        atm._bind_scan_and_detectors(obs, gain)  # H2D: boresight at both rates, offsets, bands, Mueller, gains
+        atm.set_layers()
+        atm.generate()
+        atm.synthesize_host(host_out, det0, n_det, units="K_RJ", apply_gain=True)
+
+    step(0)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.e2e_steps):
+        step(1 + i)
+    barrier()
+    dt = (time.perf_counter() - t0) / args.e2e_steps
+    if world > 1:
+        t = torch.tensor([dt], device=f"cuda:{local}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t[0])
+    checksum = float(host_out[:: max(1, n_det // 64), :: max(1, n_t // 64)].double().mean())
+    return {"value": world * n_det * n_t / dt, "unit": "detector-samples/s", "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": args.e2e_steps, "pinned_host_output": pinned,
+            "mean_K_RJ": checksum}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -326,25 +326,32 @@ class Atmosphere:
     # ---------------------------------------------------------------------------------------------------------
     def _bind_device(self, obs):
         """Create the device context and upload scan, detectors, band tables and the process matrices."""
-        ctx = self.ctx = DeviceContext(self.device, self.precision)
-        lib, dets = ctx.lib, obs.instrument.dets
+        self.ctx = DeviceContext(self.device, self.precision)
+        self._bind_scan_and_detectors(obs, None)
+        self.set_bands(obs.instrument.dets)
+        for p in self.processes.values():
+            p.bind(self.ctx)
+        self._layer_dev = {}
+
+    def _bind_scan_and_detectors(self, obs, gain):
+        """Host -> device: boresight at both rates, knot times, detector offsets / band index / Mueller / gain."""
+        ctx, dets = self.ctx, obs.instrument.dets
+        lib = ctx.lib
         bs, full = self.boresight, obs.boresight
-        az_a, el_a = _lib.f64(bs.az), _lib.f64(bs.el)
+        t_a, az_a, el_a = _lib.f64(bs.t), _lib.f64(bs.az), _lib.f64(bs.el)
         t_f, az_f, el_f = _lib.f64(full.t), _lib.f64(full.az), _lib.f64(full.el)
-        t_a = _lib.f64(bs.t)
         ctx.check(lib.matm_set_scan(ctx.h, len(bs.t), _lib.dptr(t_a), float(self.timestep), _lib.dptr(az_a), _lib.dptr(el_a),
                                     len(t_f), _lib.dptr(t_f), _lib.dptr(az_f), _lib.dptr(el_f)))
-        band_names = [b.name for b in dets.bands]
-        band_index = np.array([band_names.index(b) for b in dets.band_name], dtype=np.int32)
-        off_atm = _lib.f64(dets.offsets)
-        off_full = _lib.f64(getattr(obs, "offsets", dets.offsets))
-        mu = _lib.f64(dets.mueller00())
+        self._layers_set = False
+        if not hasattr(self, "_det_host"):
+            band_names = [b.name for b in dets.bands]
+            lut = {n: i for i, n in enumerate(band_names)}
+            self._det_host = (np.array([lut[b] for b in dets.band_name], dtype=np.int32), _lib.f64(dets.offsets),
+                              _lib.f64(getattr(obs, "offsets", dets.offsets)), _lib.f64(dets.mueller00()))
+        band_index, off_atm, off_full, mu = self._det_host
+        g = _lib.f64(gain) if gain is not None else None
         ctx.check(lib.matm_set_detectors(ctx.h, dets.n, _lib.dptr(off_atm), _lib.dptr(off_full), _lib.iptr(band_index),
-                                         _lib.dptr(mu), None))
-        self.set_bands(dets)
-        for p in self.processes.values():
-            p.bind(ctx)
-        self._layer_dev = {}
+                                         _lib.dptr(mu), _lib.dptr(g) if g is not None else None))
 
     def set_bands(self, dets):
         """Band-integrated lookup tables (band.py:235-255,264-300), evaluated on the device from the spectrum tables."""
@@ -361,12 +368,9 @@ class Atmosphere:
 
     def set_gain(self, gain):
         """Per-detector gain factors exp(gain_error N(0,1)) (simulation.py:239-241)."""
-        ctx, obs = self.ctx, self._obs
-        dets = obs.instrument.dets
-        band_names = [b.name for b in dets.bands]
-        band_index = np.array([band_names.index(b) for b in dets.band_name], dtype=np.int32)
-        off_atm, off_full = _lib.f64(dets.offsets), _lib.f64(getattr(obs, "offsets", dets.offsets))
-        mu, g = _lib.f64(dets.mueller00()), _lib.f64(gain)
+        ctx, dets = self.ctx, self._obs.instrument.dets
+        band_index, off_atm, off_full, mu = self._det_host
+        g = _lib.f64(gain)
         ctx.check(ctx.lib.matm_set_detectors(ctx.h, dets.n, _lib.dptr(off_atm), _lib.dptr(off_full), _lib.iptr(band_index),
                                              _lib.dptr(mu), _lib.dptr(g)))
 
@@ -377,44 +381,68 @@ class Atmosphere:
             raise RuntimeError("Atmosphere must be initialized with a simulation.")
         ctx, L = self.ctx, self.layers
         tc = ctx.torch
-        dets = self._obs.instrument.dets
+        cur = tc.cuda.current_stream(ctx.device)
+        fork = cur.record_event()
+        if not hasattr(self, "_streams"):
+            self._streams = {k: tc.cuda.Stream(device=ctx.device) for k in self.processes}
+        if not hasattr(self, "_layer_plan"):
+            self._build_layer_plan()
+        # one stream per process: the 8 recurrences are independent sequential chains and run side by side
         for k, process in self.processes.items():
-            if self.noise == "host":
-                process.run(rng=self.rng)
-            else:
-                process.run(seed=self.seed, subsequence=k)
-        st = ctx.stream_ptr()
-        descs = (_lib.LayerDesc * len(L["h"]))()
-        keep = []
-        n_layers = 0
+            stream = self._streams[k]
+            stream.wait_event(fork)
+            with tc.cuda.stream(stream):
+                if self.noise == "host":
+                    process.run(rng=self.rng)
+                else:
+                    process.run(seed=self.seed, subsequence=k)
+                st = ctx.stream_ptr()
+                for (li, col0, n_cols, sig_e, sig_x) in self._layer_plan[k]:
+                    out, scratch = self._layer_dev[li]
+                    ctx.check(ctx.lib.matm_smooth_layer(ctx.h, process.values_device.data_ptr(), process.n_extrusion,
+                                                        process.n_cross_section, col0, n_cols, sig_e, sig_x,
+                                                        out.data_ptr(), scratch.data_ptr(), st))
+            cur.wait_stream(stream)
+        if not getattr(self, "_layers_set", False):
+            self.set_layers()
+        self._generated = True
+
+    def _build_layer_plan(self):
+        """Per layer: its columns in the process, the beam-smoothing widths in cells (atmosphere.py:328-339) and the
+        device buffers (smoothed layer in the context's dtype + float64 scratch)."""
+        ctx, L, dets = self.ctx, self.layers, self._obs.instrument.dets
+        self._layer_plan = {}
         for k, process in self.processes.items():
-            vx, vy = _lib.f64(process.vx), _lib.f64(process.vy)
-            keep += [vx, vy]
+            plan = []
             for li in process.layer_index:
                 cols = np.where(process.labels == li)[0]
                 col0, n_cols = int(cols[0]), len(cols)
                 beam_sigma = host.gaussian_beam_physical_fwhm(dets.primary_size, L["z"][li], dets.band_center).mean() / 2.355
-                sig_e, sig_x = beam_sigma / process.extrusion_res, beam_sigma / L["res"][li]  # :328-339
-                if li not in self._layer_dev:
-                    self._layer_dev[li] = (ctx.empty((process.n_extrusion, n_cols)),
-                                           ctx.empty((process.n_extrusion, n_cols), tc.float64))
-                out, scratch = self._layer_dev[li]
-                ctx.check(ctx.lib.matm_smooth_layer(ctx.h, process.values_device.data_ptr(), process.n_extrusion,
-                                                    process.n_cross_section, col0, n_cols, float(sig_e), float(sig_x),
-                                                    out.data_ptr(), scratch.data_ptr(), st))
+                plan.append((int(li), col0, n_cols, float(beam_sigma / process.extrusion_res), float(beam_sigma / L["res"][li])))
+                self._layer_dev[int(li)] = (ctx.empty((process.n_extrusion, n_cols)),
+                                            ctx.empty((process.n_extrusion, n_cols), ctx.torch.float64))
+            self._layer_plan[k] = plan
+
+    def set_layers(self):
+        """Hand the layer geometry (height, transform, grids, wind) and the device layers to the sampler."""
+        ctx, L = self.ctx, self.layers
+        descs = (_lib.LayerDesc * len(L["h"]))()
+        keep, n_layers = [], 0
+        for k, process in self.processes.items():
+            vx, vy = _lib.f64(process.vx), _lib.f64(process.vy)
+            keep += [vx, vy]
+            for (li, col0, n_cols, _, _) in self._layer_plan[k]:
                 d = descs[n_layers]
-                d.data_dev, d.n_ext, d.n_cs = out.data_ptr(), process.n_extrusion, n_cols
+                d.data_dev, d.n_ext, d.n_cs = self._layer_dev[li][0].data_ptr(), process.n_extrusion, n_cols
                 d.h, d.pwv_rms = float(L["h"][li]), float(L["pwv_rms"][li])
                 d.transform = (C.c_double * 9)(*np.asarray(process.transform, dtype=float).ravel())
                 d.ext0, d.ext_step = float(process.extrusion[0]), float(process.extrusion_res)
-                xs = process.cross_section[cols, 0]
+                xs = process.cross_section[col0:col0 + n_cols, 0]
                 d.cs0, d.cs_last = float(xs[0]), float(xs[-1])
                 d.vx_host, d.vy_host = _lib.dptr(vx), _lib.dptr(vy)
                 n_layers += 1
-        if not getattr(self, "_layers_set", False):
-            ctx.check(ctx.lib.matm_set_layers(ctx.h, n_layers, descs, float(self.weather.pwv)))
-            self._layers_set = True
-        self._generated = True
+        ctx.check(ctx.lib.matm_set_layers(ctx.h, n_layers, descs, float(self.weather.pwv)))
+        self._layers_set = True
 
     def smoothed_layer(self, li):
         """Beam-smoothed layer ``li`` as a host array (validation helper)."""
@@ -427,6 +455,26 @@ class Atmosphere:
         out = ctx.empty((n_det, len(self.boresight.t)), ctx.torch.float64)
         ctx.check(ctx.lib.matm_zenith_pwv(ctx.h, det0, n_det, out.data_ptr(), ctx.stream_ptr()))
         return out
+
+    def synthesize(self, det0=0, n_det=None, units="K_RJ", apply_gain=True, out=None):
+        """The fused kernel (a6..a14): (n_det, n_t) TOD of the atmosphere field on the device, in the context's dtype."""
+        ctx = self.ctx
+        n_det = self._obs.instrument.dets.n - det0 if n_det is None else n_det
+        if out is None:
+            out = ctx.empty((n_det, len(self._obs.boresight.t)))
+        ctx.check(ctx.lib.matm_synthesize(ctx.h, det0, n_det, out.data_ptr(), _lib.UNITS_KRJ if units == "K_RJ" else _lib.UNITS_PW,
+                                          1 if apply_gain else 0, ctx.stream_ptr()))
+        return out
+
+    def synthesize_host(self, out_host, det0=0, n_det=None, units="K_RJ", apply_gain=True):
+        """Same, delivered into a host tensor / ndarray (pinned for full PCIe speed); returns when the data has landed."""
+        ctx = self.ctx
+        n_det = self._obs.instrument.dets.n - det0 if n_det is None else n_det
+        ptr = out_host.data_ptr() if hasattr(out_host, "data_ptr") else out_host.ctypes.data
+        ctx.torch.cuda.current_stream(ctx.device).synchronize()  # the staging streams do not follow torch's stream
+        ctx.check(ctx.lib.matm_synthesize_host(ctx.h, det0, n_det, ptr, _lib.UNITS_KRJ if units == "K_RJ" else _lib.UNITS_PW,
+                                               1 if apply_gain else 0))
+        return out_host
 
     def simulate_pwv(self, instrument=None):
         """atmosphere.py:293-380.  Generates the layers; ``zenith_scaled_pwv`` is evaluated when read."""

@@ -75,16 +75,10 @@ class AtmosphereMixin:
 
         obs.zenith_scaled_pwv = LazyArray((n_det, n_t), np.float64, upsampled)
 
-    def _compute_atmospheric_loading(self, obs, det0=0, n_det=None, units="pW", apply_gain=False):
+    def _compute_atmospheric_loading(self, obs, det0=0, n_det=None, units="pW", apply_gain=False, out=None):
         """(n_det, n_t) loading [pW] in ``self.dtype`` on the device (:39-84): emission lookup x Mueller[0, 0] at the
         atmosphere rate, cubic (not-a-knot) upsample to the full rate."""
-        atm = obs.atmosphere
-        ctx = atm.ctx
-        n_det = obs.instrument.dets.n - det0 if n_det is None else n_det
-        out = ctx.empty((n_det, len(obs.boresight.t)))
-        ctx.check(ctx.lib.matm_synthesize(ctx.h, det0, n_det, out.data_ptr(), _lib.UNITS_KRJ if units == "K_RJ" else _lib.UNITS_PW,
-                                          1 if apply_gain else 0, ctx.stream_ptr()))
-        return out
+        return obs.atmosphere.synthesize(det0, n_det, units=units, apply_gain=apply_gain, out=out)
 
 
 class Simulation(AtmosphereMixin):

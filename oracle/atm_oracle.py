@@ -609,3 +609,24 @@ def simulate(instrument, plan, site, weather, spectrum, rng, model="2d", f32=Fal
     loading, metadata = run_obs(obs, atm, rng, dtype=dtype, record=record)
     tod = tod_to_K_RJ(loading, obs, atm, metadata, out_dtype=dtype)
     return dict(obs=obs, atmosphere=atm, loading_pW=loading, tod_K_RJ=tod, metadata=metadata)
+
+
+def atmosphere_from_geometry(weather, spectrum, layers, timestep, boresight_t, boresight_az, boresight_el, det_offsets,
+                             processes, f32=False):
+    """An initialised oracle ``Atmosphere`` from already-computed set-up geometry (layer table, downsampled boresight,
+    per-process stencil / A / B / transform), so that the CPU baseline of ``bench.py`` times stages a5-a14 without
+    repeating the footprint optimisation at 100k-detector scale.  ``processes``: {k: dict(cross_section, extrusion, A, B,
+    transform, vx, vy, layer_index, labels, extrusion_res)}."""
+    atm = Atmosphere(weather, spectrum, f32=f32)
+    atm.layers, atm.timestep = layers, timestep
+    atm.boresight = Coords(boresight_t, boresight_az, boresight_el, f32)
+    atm.coords = atm.boresight.broadcast(det_offsets)
+    atm.processes = {}
+    for k, g in processes.items():
+        p = AutoregressiveProcess(g["cross_section"], g["extrusion"], {}, jitter=1e-8)
+        p.A, p.B = g["A"], g["B"]
+        p.transform, p.vx, p.vy = g["transform"], g["vx"], g["vy"]
+        p.layer_index, p.labels, p.extrusion_res = g["layer_index"], g["labels"], g["extrusion_res"]
+        atm.processes[k] = p
+    atm._initialized = True
+    return atm
