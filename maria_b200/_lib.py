@@ -34,7 +34,7 @@ SIGNATURES = {
     "matm_last_error": (C.c_int, [vp, C.c_char_p, C.c_int]),
     "matm_abi_version": (C.c_int, []),
     "matm_fill_normal": (C.c_int, [vp, vp, C.c_size_t, C.c_uint64, C.c_uint64, vp]),
-    "matm_ar_generate": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp]),
+    "matm_ar_generate": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp, vp]),
     "matm_smooth_layer": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, vp, vp, vp]),
     "matm_set_scan": (C.c_int, [vp, C.c_int, c_dp, C.c_double, c_dp, c_dp, C.c_int64, c_dp, c_dp, c_dp]),
     "matm_set_layers": (C.c_int, [vp, C.c_int, C.POINTER(LayerDesc), C.c_double]),

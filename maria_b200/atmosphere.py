@@ -105,6 +105,9 @@ class AutoregressiveProcess:
         self.sample_points = np.c_[self.extrusion[self.extrusion_sample_index],
                                    self.cross_section[self.cross_section_sample_index]]  # process.py:72-89
         self.n_sample = len(self.sample_points)
+        esi = self.extrusion_sample_index
+        # leading samples on the three most recent rows (esi is non-decreasing by construction)
+        self.n_near = int(np.sum(esi + 1 <= 3)) if np.all(np.diff(esi) >= 0) else -1
         self.live_edge_points = np.c_[
             self.extrusion[0] * np.ones(self.n_cross_section) - np.gradient(self.extrusion).mean(),
             self.cross_section]  # process.py:91-100
@@ -155,7 +158,7 @@ class AutoregressiveProcess:
                 raise ValueError("either a host rng or a Philox seed is required")
             ctx.check(ctx.lib.matm_fill_normal(ctx.h, tail.data_ptr(), tail.numel(), seed, 2 * subsequence, st))
             ctx.check(ctx.lib.matm_fill_normal(ctx.h, dv["z"].data_ptr(), dv["z"].numel(), seed, 2 * subsequence + 1, st))
-        ctx.check(ctx.lib.matm_ar_generate(ctx.h, n_ext, n_cs, self.n_sample, dv["A"].data_ptr(), dv["B"].data_ptr(),
+        ctx.check(ctx.lib.matm_ar_generate(ctx.h, n_ext, n_cs, self.n_sample, self.n_near, dv["A"].data_ptr(), dv["B"].data_ptr(),
                                            dv["esi"].data_ptr(), dv["csi"].data_ptr(), dv["buffer"].data_ptr(),
                                            dv["z"].data_ptr(), st))
         self._values_host = None

@@ -184,7 +184,206 @@ static int launch_chain(matm_handle* h, const double* A, const int* esi, const i
   return MATM_OK;
 }
 
-extern "C" int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sample, const double* A_dev,
+// ---------------------------------------------------------------------------------------------------------
+// The chain, latency-optimised (v2).  What bounds a step is not arithmetic but the round trips on its critical path,
+// so everything that is not the previous row is taken off that path:
+//   * A lives in REGISTERS: warp w of CTA c owns RW rows, lane l holds their entries for samples l, l+32, ...;
+//   * the last three rows (stencil offsets 1..3) live in a 4-slot shared-memory ring (row R -> slot R & 3), written
+//     by the owners of each element -- through distributed shared memory into every CTA of the cluster;
+//   * stencil rows further back (offsets >= 4) and the row's own B z term are read from L2 two steps ahead of their
+//     use (register pipeline of depth 2), so their latency never shows;
+//   * one barrier per step: __syncthreads (1 CTA) or the hardware cluster barrier.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void st_dsmem_f64(double* local_ptr, int cta, double v) {
+  uint32_t a = smem_u32(local_ptr), r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(cta));
+  asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(r), "d"(v) : "memory");
+}
+
+template <int RW, int M>
+__global__ void __launch_bounds__(AR_THREADS, 1)
+    ar_chain_v2_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
+                       double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* hist = reinterpret_cast<double*>(smem_raw);  // [4][n_cs]
+  const int n_far = n_sample - n_near;
+  double* far = hist + 4 * (size_t)n_cs;               // [2][n_far]
+  int cta = 0;
+  if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
+  const int rpc = (n_cs + cl - 1) / cl;
+  const int row0 = cta * rpc;
+  const int rows = max(0, min(n_cs, row0 + rpc) - row0);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  // ---- per-thread constants: A entries and the stencil descriptors of this lane's samples ----
+  double a[RW][M];
+  int desc[M];  // near sample: (offset << 24) | column ; far sample: index among the far samples ; -1: none
+#pragma unroll
+  for (int m = 0; m < M; m++) {
+    const int s = lane + 32 * m;
+    desc[m] = -1;
+    if (s < n_sample) desc[m] = s < n_near ? (((esi[s] + 1) << 24) | csi[s]) : (s - n_near);
+#pragma unroll
+    for (int rr = 0; rr < RW; rr++) {
+      const int r = warp * RW + rr;
+      a[rr][m] = (s < n_sample && r < rows) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
+    }
+  }
+  // far sample f handled by thread f (f < n_far <= AR_THREADS * 2): global offset relative to the row being computed
+  int foff[2];
+#pragma unroll
+  for (int q = 0; q < 2; q++) {
+    const int f = tid + q * AR_THREADS;
+    foff[q] = f < n_far ? (esi[n_near + f] + 1) * n_cs + csi[n_near + f] : -1;
+  }
+
+  const int i_top = 2 * n_ext - 1;
+  // ---- prologue: ring <- rows i_top+1 .. i_top+3 (initial noise); far buffers and pipelines for the first steps ----
+  for (int e = tid; e < 3 * n_cs; e += AR_THREADS) {
+    const int R = i_top + 1 + e / n_cs, c = e % n_cs;
+    hist[(R & 3) * n_cs + c] = buffer[(size_t)R * n_cs + c];
+  }
+#pragma unroll
+  for (int q = 0; q < 2; q++)
+    if (foff[q] >= 0) {
+      const int f = tid + q * AR_THREADS;
+      far[(i_top & 1) * n_far + f] = buffer[(size_t)i_top * n_cs + foff[q]];
+      if (i_top >= 1) far[((i_top - 1) & 1) * n_far + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
+    }
+  double far_p[2] = {0.0, 0.0};  // in flight: far values of step i - 2, loaded during step i
+  double bz_p1[RW], bz_p2[RW];   // B z of the rows of step i - 1 / i - 2
+#pragma unroll
+  for (int rr = 0; rr < RW; rr++) {
+    const int r = warp * RW + rr;
+    bz_p1[rr] = bz_p2[rr] = 0.0;
+    if (r < rows) {
+      bz_p1[rr] = buffer[(size_t)i_top * n_cs + row0 + r];
+      if (i_top >= 1) bz_p2[rr] = buffer[(size_t)(i_top - 1) * n_cs + row0 + r];
+    }
+  }
+  __syncthreads();
+  if (cl > 1) cluster_barrier();
+
+  for (int i = i_top; i >= 0; i--) {
+    // (1) issue the far / B z loads of step i - 2 (rows >= i + 2, complete since two barriers ago)
+    double far_n[2] = {0.0, 0.0}, bz_n[RW];
+    if (i >= 2) {
+#pragma unroll
+      for (int q = 0; q < 2; q++)
+        if (foff[q] >= 0) far_n[q] = __ldcg(buffer + (size_t)(i - 2) * n_cs + foff[q]);
+#pragma unroll
+      for (int rr = 0; rr < RW; rr++) {
+        const int r = warp * RW + rr;
+        bz_n[rr] = r < rows ? __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r) : 0.0;
+      }
+    } else {
+#pragma unroll
+      for (int rr = 0; rr < RW; rr++) bz_n[rr] = 0.0;
+    }
+    // (2) the dot products of this step, A from registers, x from shared memory
+    double acc[RW];
+#pragma unroll
+    for (int rr = 0; rr < RW; rr++) acc[rr] = 0.0;
+    const double* farp = far + (i & 1) * n_far;
+#pragma unroll
+    for (int m = 0; m < M; m++) {
+      const int d = desc[m];
+      double x = 0.0;
+      if (d >= 0) {
+        const int off = d >> 24;
+        x = off ? hist[((i + off) & 3) * n_cs + (d & 0xffffff)] : farp[d];
+      }
+#pragma unroll
+      for (int rr = 0; rr < RW; rr++) acc[rr] = fma(a[rr][m], x, acc[rr]);
+    }
+#pragma unroll
+    for (int rr = 0; rr < RW; rr++) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc[rr] += __shfl_xor_sync(0xffffffffu, acc[rr], o);
+    }
+    // (3) publish: lane rr of the warp writes row warp*RW+rr to the ring of every CTA and to global memory
+#pragma unroll
+    for (int rr = 0; rr < RW; rr++) {
+      const int r = warp * RW + rr;
+      if (lane == rr && r < rows) {
+        const double v = bz_p1[rr] + acc[rr];
+        double* slot = hist + (i & 3) * n_cs + row0 + r;
+        if (cl == 1) {
+          *slot = v;
+        } else {
+          for (int c = 0; c < cl; c++) st_dsmem_f64(slot, c, v);
+        }
+        buffer[(size_t)i * n_cs + row0 + r] = v;
+      }
+    }
+    // (4) land the far values loaded one step ago (they belong to step i - 1) and rotate the pipelines
+    if (i >= 1) {
+#pragma unroll
+      for (int q = 0; q < 2; q++)
+        if (foff[q] >= 0 && i <= i_top - 1) far[((i - 1) & 1) * n_far + tid + q * AR_THREADS] = far_p[q];
+    }
+#pragma unroll
+    for (int q = 0; q < 2; q++) far_p[q] = far_n[q];
+#pragma unroll
+    for (int rr = 0; rr < RW; rr++) {
+      bz_p1[rr] = bz_p2[rr];
+      bz_p2[rr] = bz_n[rr];
+    }
+    if (cl == 1)
+      __syncthreads();
+    else
+      cluster_barrier();
+  }
+}
+
+template <int RW, int M>
+static int launch_chain_v2(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
+                           int n_cs, int n_sample, int n_near, int cl, cudaStream_t stream) {
+  const size_t smem = (4 * (size_t)n_cs + 2 * (size_t)(n_sample - n_near)) * sizeof(double) + 16;
+  MATM_CUDA(h, cudaFuncSetAttribute(ar_chain_v2_kernel<RW, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cl, 1, 1);
+  cfg.blockDim = dim3(AR_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cl;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, ar_chain_v2_kernel<RW, M>, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl));
+  h->launches++;
+  return MATM_OK;
+}
+
+// picks (cluster size, rows per warp, samples per lane) for the register-resident kernel; false if it does not fit
+static bool plan_v2(int n_cs, int n_sample, int* cl, int* rw, int* m) {
+  const int warps = AR_THREADS / 32;
+  int mm = (n_sample + 31) / 32;
+  mm = mm <= 4 ? 4 : mm <= 8 ? 8 : mm <= 12 ? 12 : mm <= 16 ? 16 : 0;
+  if (!mm) return false;
+  const int max_rw = mm <= 8 ? 4 : 2;  // RW * M <= 32 doubles of A per thread (no spills at 512 threads)
+  for (int c = 1; c <= 8; c *= 2) {
+    const int rpc = (n_cs + c - 1) / c;
+    int r = (rpc + warps - 1) / warps;
+    r = r <= 1 ? 1 : r <= 2 ? 2 : r <= 4 ? 4 : 0;
+    if (r && r <= max_rw) {
+      *cl = c;
+      *rw = r;
+      *m = mm;
+      return true;
+    }
+  }
+  return false;
+}
+
+extern "C" int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sample, int n_near, const double* A_dev,
                                 const double* B_dev, const int32_t* esi_dev, const int32_t* csi_dev,
                                 double* buffer_dev, const double* z_dev, void* stream) {
   MATM_CHECK_HANDLE(h);
@@ -199,7 +398,19 @@ extern "C" int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sampl
   bz_gemm_kernel<<<grid, 256, 0, st>>>(z_dev, B_dev, buffer_dev, M, n_cs);
   MATM_LAUNCHED(h);
 
-  // smallest cluster whose per-CTA slice of A fits in shared memory; above 8 CTAs A streams from L2
+  // register-resident kernel when the process fits it
+  {
+    int cl2, rw, mm;
+    if (n_near >= 0 && n_near <= n_sample && n_ext >= 4 && (n_sample - n_near) <= 2 * AR_THREADS && plan_v2(n_cs, n_sample, &cl2, &rw, &mm)) {
+#define V2_CASE(RWV, MV) \
+  if (rw == RWV && mm == MV) \
+    return launch_chain_v2<RWV, MV>(h, A_dev, esi_dev, csi_dev, buffer_dev, n_ext, n_cs, n_sample, n_near, cl2, st);
+      V2_CASE(1, 4) V2_CASE(2, 4) V2_CASE(4, 4) V2_CASE(1, 8) V2_CASE(2, 8) V2_CASE(4, 8)
+      V2_CASE(1, 12) V2_CASE(2, 12) V2_CASE(1, 16) V2_CASE(2, 16)
+#undef V2_CASE
+    }
+  }
+  // fallback (v1): smallest cluster whose per-CTA slice of A fits in shared memory; above 8 CTAs A streams from L2
   const size_t budget = 200 * 1024;
   const size_t fixed = (size_t)n_sample * (sizeof(double) + sizeof(int)) + 64;
   int cl = 1, a_in_smem = 0;

@@ -49,6 +49,13 @@ struct SynthParams {
   const double* side_el;   // (nel,)
   const double* G2;        // (n_bands, npwv, nel) emission grid folded at T0 [pW]
   const double* H1;        // (n_bands, nel) transmission integral folded at (cal_T0, cal_pwv), times factor*k_B*1e12
+  // the same tables in the handle's arithmetic type R (float or double), read by the kernels
+  const void* pwv_R;       // (npwv,)
+  const void* el_R;        // (nel,)
+  const void* sinel_R;     // (nel,): sin(side_el), 2.0 where side_el >= pi/2 (search key for sin(el))
+  const void* G2_R;        // (n_bands, npwv, nel)
+  const void* Hc_R;        // (n_bands, nel-1): H(el) = Hc + Hs * el on el-interval i  (same line as the lerp of H1)
+  const void* Hs_R;        // (n_bands, nel-1)
   int table_ok;            // 0 if T0 / cal_T0 / cal_pwv left the table (results are NaN, as the reference)
   int* flags;              // [0] = status bits, [1] = layer, [2..3] = det (lo, hi), [4..5] = sample (lo, hi)
 };
@@ -69,6 +76,7 @@ struct matm_handle {
   double *det_atm = nullptr, *det_full = nullptr, *mueller00 = nullptr, *gain = nullptr;
   int32_t* band_index = nullptr;
   double *side_pwv = nullptr, *side_el = nullptr, *G2 = nullptr, *H1 = nullptr;
+  void* tabR = nullptr;  // one allocation holding the R-typed tables
   int* flags = nullptr;
   std::vector<double> az_atm_host, el_atm_host;
   // e2e staging

@@ -47,6 +47,7 @@ extern "C" int matm_destroy(matm_handle* h) {
   cudaFree(h->side_el);
   cudaFree(h->G2);
   cudaFree(h->H1);
+  cudaFree(h->tabR);
   cudaFree(h->flags);
   for (int i = 0; i < 2; i++) {
     cudaFree(h->stage_dev[i]);

@@ -330,6 +330,32 @@ __global__ void fold_tables_kernel(const double* __restrict__ emission, const do
   }
 }
 
+// R-typed copies of the lookup tables, laid out back to back: pwv | el | sin el | G2 | Hc | Hs
+template <typename R>
+__global__ void typed_tables_kernel(const double* __restrict__ pwv, const double* __restrict__ el,
+                                    const double* __restrict__ G2, const double* __restrict__ H1, int n_bands, int npwv,
+                                    int nel, R* __restrict__ out) {
+  R* o_pwv = out;
+  R* o_el = o_pwv + npwv;
+  R* o_sin = o_el + nel;
+  R* o_G2 = o_sin + nel;
+  R* o_Hc = o_G2 + (size_t)n_bands * npwv * nel;
+  R* o_Hs = o_Hc + (size_t)n_bands * (nel - 1);
+  int t = blockIdx.x * blockDim.x + threadIdx.x, nt = gridDim.x * blockDim.x;
+  for (int i = t; i < npwv; i += nt) o_pwv[i] = (R)pwv[i];
+  for (int i = t; i < nel; i += nt) {
+    o_el[i] = (R)el[i];
+    o_sin[i] = el[i] >= M_PI / 2 ? (R)2 : (R)sin(el[i]);
+  }
+  for (int i = t; i < n_bands * npwv * nel; i += nt) o_G2[i] = (R)G2[i];
+  for (int i = t; i < n_bands * (nel - 1); i += nt) {
+    int b = i / (nel - 1), e = i % (nel - 1);
+    double slope = (H1[b * nel + e + 1] - H1[b * nel + e]) / (el[e + 1] - el[e]);
+    o_Hs[i] = (R)slope;
+    o_Hc[i] = (R)(H1[b * nel + e] - slope * el[e]);
+  }
+}
+
 extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int nel, int nnu, const double* side_T_host,
                               const double* side_pwv_host, const double* side_el_host, const double* side_nu_host,
                               const double* emission_host, const double* opacity_host, const double* passband_host,
@@ -364,6 +390,16 @@ extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int
   fold_tables_kernel<<<(total + 127) / 128, 128>>>(em, op, pb, nu, n_bands, nT, npwv, nel, nnu, iT, wT, iTc, wTc, iPc, wPc,
                                                    cs, h->G2, h->H1);
   MATM_LAUNCHED(h);
+  const size_t n_tab = (size_t)npwv + 2 * nel + (size_t)n_bands * npwv * nel + 2 * (size_t)n_bands * (nel - 1);
+  const size_t esz = h->dtype == MATM_F64 ? 8 : 4;
+  if (h->tabR) MATM_CUDA(h, cudaFree(h->tabR));
+  h->tabR = nullptr;
+  MATM_CUDA(h, cudaMalloc(&h->tabR, n_tab * esz));
+  if (h->dtype == MATM_F64)
+    typed_tables_kernel<double><<<8, 256>>>(h->side_pwv, h->side_el, h->G2, h->H1, n_bands, npwv, nel, (double*)h->tabR);
+  else
+    typed_tables_kernel<float><<<8, 256>>>(h->side_pwv, h->side_el, h->G2, h->H1, n_bands, npwv, nel, (float*)h->tabR);
+  MATM_LAUNCHED(h);
   MATM_CUDA(h, cudaDeviceSynchronize());
   cudaFree(em);
   cudaFree(op);
@@ -378,6 +414,15 @@ extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int
   P.side_el = h->side_el;
   P.G2 = h->G2;
   P.H1 = h->H1;
+  {
+    char* base = (char*)h->tabR;
+    P.pwv_R = base;
+    P.el_R = base + esz * (size_t)npwv;
+    P.sinel_R = base + esz * ((size_t)npwv + nel);
+    P.G2_R = base + esz * ((size_t)npwv + 2 * nel);
+    P.Hc_R = base + esz * ((size_t)npwv + 2 * nel + (size_t)n_bands * npwv * nel);
+    P.Hs_R = base + esz * ((size_t)npwv + 2 * nel + (size_t)n_bands * npwv * nel + (size_t)n_bands * (nel - 1));
+  }
   P.table_ok = (ok ? 1 : 0) | (okc ? 2 : 0);
   h->have_bands = true;
   return MATM_OK;

@@ -22,13 +22,14 @@ __global__ void __launch_bounds__(SY_THREADS) zenith_pwv_kernel(const __grid_con
                                                                 int64_t n_det, double* __restrict__ out) {
   constexpr int W = 128;
   __shared__ Knot<R> knots[W];
+  __shared__ LayerS<R> ls[MATM_MAX_LAYERS];
   extern __shared__ __align__(16) unsigned char dyn[];
   LayerKnot<R>* lk = reinterpret_cast<LayerKnot<R>*>(dyn);
   const int n_ttiles = (P.n_t_atm + W - 1) / W;
   const int64_t dtile = blockIdx.x / n_ttiles;
   const int ttile = blockIdx.x % n_ttiles;
   const int wa = ttile * W, Wn = min(W, P.n_t_atm - wa);
-  load_window<R>(P, wa, Wn, W, knots, lk);
+  load_window<R>(P, wa, Wn, W, knots, lk, ls);
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t d = dtile * DT + lane;
@@ -37,7 +38,7 @@ __global__ void __launch_bounds__(SY_THREADS) zenith_pwv_kernel(const __grid_con
   const R u = (R)da[0], Y = (R)da[1], wm1 = (R)da[2];
   for (int k = warp; k < Wn; k += SY_THREADS / 32) {
     R sin_el;
-    R z = sample_zenith_pwv<R>(P, u, Y, wm1, knots[k], lk + k, W, det0 + d, wa + k, &sin_el);
+    R z = sample_zenith_pwv<R>(P, P.n_layers, ls, u, Y, wm1, knots[k], lk + k, W, det0 + d, wa + k, &sin_el);
     out[d * P.n_t_atm + wa + k] = (double)z;
   }
 }
@@ -71,21 +72,27 @@ __global__ void __launch_bounds__(256) upsample_linear_kernel(const __grid_const
 //   phase 3: evaluate at the full-rate samples of the tile, gain, calibration, one store per sample
 // ---------------------------------------------------------------------------------------------------------
 template <typename R>
+struct YM {  // knot value and spline second derivative (times the detector gain), interleaved: one 8/16-byte load
+  R y, m;
+};
+
+template <typename R>
 __global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant__ SynthParams P, int64_t det0,
                                                            int64_t n_det, R* __restrict__ out, int units,
                                                            int apply_gain) {
   using T = Tile<R>;
   extern __shared__ __align__(16) unsigned char dyn[];
-  R* y = reinterpret_cast<R*>(dyn);                       // [DT][WP]
-  R* m = y + DT * T::WP;                                  // [DT][WP]
-  R* spl = m + DT * T::WP;                                // [W][5] spline system of the window (see SynthParams::spl)
+  YM<R>* ym = reinterpret_cast<YM<R>*>(dyn);              // [DT][WP]
+  R* spl = reinterpret_cast<R*>(ym + DT * T::WP);         // [W][5] spline system of the window (see SynthParams::spl)
   Knot<R>* knots = reinterpret_cast<Knot<R>*>(spl + 5 * T::W);
   LayerKnot<R>* lk = reinterpret_cast<LayerKnot<R>*>(knots + T::W);  // [n_layers][W]
+  __shared__ LayerS<R> ls[MATM_MAX_LAYERS];
   __shared__ R dc_u[DT], dc_w[DT], dc_gain[DT];
-  __shared__ int dc_band[DT];
+  __shared__ int dc_hoff[DT];
 
   const int n = P.n_t_atm;
   const int n_int = n - 1;  // spline intervals
+  const int n_layers = P.n_layers;
   const int n_ttiles = (n_int + T::KT - 1) / T::KT;
   const int64_t dtile = blockIdx.x / n_ttiles;
   const int ttile = blockIdx.x % n_ttiles;
@@ -96,7 +103,7 @@ __global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant
   const int64_t dbase = dtile * DT;  // relative to det0
   const int nd = (int)min((int64_t)DT, n_det - dbase);
 
-  load_window<R>(P, wa, Wn, T::W, knots, lk);
+  load_window<R>(P, wa, Wn, T::W, knots, lk, ls);
   if (threadIdx.x < DT) {
     int dd = threadIdx.x;
     if (dd < nd) {
@@ -104,57 +111,72 @@ __global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant
       dc_u[dd] = (R)P.det_full[2 * d];
       dc_w[dd] = (R)P.det_full[2 * d + 1];
       dc_gain[dd] = apply_gain ? (R)P.gain[d] : (R)1;
-      dc_band[dd] = P.band_index[d];
+      dc_hoff[dd] = P.band_index[d] * (P.nel - 1);
     }
   }
   for (int e = threadIdx.x; e < 5 * Wn; e += SY_THREADS) spl[e] = (R)P.spl[5 * (size_t)wa + e];
   __syncthreads();
 
-  // ---- phase 1 ----
+  // ---- phase 1: loading [pW] at the window's knots; lane = detector, the warps stride over the knots ----
   if (lane < nd) {
     const int64_t d = det0 + dbase + lane;
     const double* da = P.det_atm + 4 * d;
     const R u = (R)da[0], Y = (R)da[1], wm1 = (R)da[2];
     const int band = P.band_index[d];
     const R mu = (R)P.mueller00[d];
+    int ip = 0, ie = 0;
     for (int k = warp; k < Wn; k += SY_THREADS / 32) {
       R sin_el;
-      R z = sample_zenith_pwv<R>(P, u, Y, wm1, knots[k], lk + k, T::W, d, wa + k, &sin_el);
-      y[lane * T::WP + k] = loading_pW<R>(P, band, mu, z, sin_el);
+      R z = sample_zenith_pwv<R>(P, n_layers, ls, u, Y, wm1, knots[k], lk + k, T::W, d, wa + k, &sin_el);
+      ym[lane * T::WP + k].y = loading_pW<R>(P, band, mu, z, sin_el, ip, ie);
     }
   }
   __syncthreads();
 
   // ---- phase 2: second derivatives M_k of the not-a-knot cubic spline through the window's knots ----
-  // Rows glo..ghi of the global tridiagonal system, swept with the global elimination factors.  At a true end of the
-  // series the sweep starts / ends exactly; at an artificial end it starts from the locally-constant guess
-  // M = d / (a + b + c), whose error decays by ~(2 - sqrt 3) per knot across the halo.
+  // Rows of the global tridiagonal system, swept with the global elimination factors.  At a true end of the series
+  // the sweep starts / ends exactly; at an artificial end it starts from the locally-constant guess
+  // M = d / (a + b + c), whose error decays by ~(2 - sqrt 3) per knot across the halo.  The gain multiplies y and M
+  // at the end (the spline is linear in the data), so phase 3 does not have to.
   if (warp == 0 && lane < nd) {
-    R* yy = y + lane * T::WP;
-    R* mm = m + lane * T::WP;
+    YM<R>* row = ym + lane * T::WP;
     const int lo = 1, hi = Wn - 2;  // local rows; global row = wa + local
+    auto yv = [&](int k) { return row[k].y; };
     auto invh = [&](int k) { return spl[5 * k + 0]; };
-    auto rhs = [&](int k) { return (R)6 * ((yy[k + 1] - yy[k]) * invh(k) - (yy[k] - yy[k - 1]) * invh(k - 1)); };
+    auto rhs = [&](int k) { return (R)6 * ((yv(k + 1) - yv(k)) * invh(k) - (yv(k) - yv(k - 1)) * invh(k - 1)); };
     auto guess = [&](int k) { return rhs(k) / ((R)3 * ((R)1 / invh(k - 1) + (R)1 / invh(k))); };
     R dp = (wa == 0) ? rhs(lo) * spl[5 * lo + 2] : guess(lo) * ((R)1 + spl[5 * lo + 4]);
-    mm[lo] = dp;
+    row[lo].m = dp;
     for (int k = lo + 1; k <= hi; k++) {
       dp = rhs(k) * spl[5 * k + 2] - spl[5 * k + 3] * dp;
-      mm[k] = dp;
+      row[k].m = dp;
     }
-    if (wb != n - 1) mm[hi] -= spl[5 * hi + 4] * guess(hi);
-    for (int k = hi - 1; k >= lo; k--) mm[k] -= spl[5 * k + 4] * mm[k + 1];
-    mm[0] = (wa == 0) ? mm[1] - (invh(1) / invh(0)) * (mm[2] - mm[1]) : mm[1];
-    mm[Wn - 1] = (wb == n - 1) ? mm[Wn - 2] + (invh(Wn - 3) / invh(Wn - 2)) * (mm[Wn - 2] - mm[Wn - 3]) : mm[Wn - 2];
+    if (wb != n - 1) row[hi].m -= spl[5 * hi + 4] * guess(hi);
+    for (int k = hi - 1; k >= lo; k--) row[k].m -= spl[5 * k + 4] * row[k + 1].m;
+    row[0].m = (wa == 0) ? row[1].m - (invh(1) / invh(0)) * (row[2].m - row[1].m) : row[1].m;
+    row[Wn - 1].m = (wb == n - 1) ? row[Wn - 2].m + (invh(Wn - 3) / invh(Wn - 2)) * (row[Wn - 2].m - row[Wn - 3].m)
+                                  : row[Wn - 2].m;
+    const R g = dc_gain[lane];
+    for (int k = 0; k < Wn; k++) {
+      row[k].y *= g;
+      row[k].m *= g;
+    }
   }
   __syncthreads();
 
-  // ---- phase 3 ----
+  // ---- phase 3: evaluate at the full-rate samples of the tile; thread = sample, loop over the tile's detectors ----
   const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
+  const double t_atm0 = P.t_atm0, inv_ts = 1.0 / P.timestep;
+  const int64_t n_t = P.n_t;
+  const bool krj = units == MATM_UNITS_KRJ;
+  const R* sing = reinterpret_cast<const R*>(P.sinel_R);
+  const R* hcs = reinterpret_cast<const R*>(P.Hc_R);
+  const R* hss = reinterpret_cast<const R*>(P.Hs_R);
+  int ie = 0;
   for (int64_t j = j0 + threadIdx.x; j < j1; j += SY_THREADS) {
     const double tj = P.t_full[j];
-    int i = (int)floor((tj - P.t_atm0) / P.timestep);  // the interval this tile was assigned (jstart uses the same rule)
-    i = min(max(i, 0), n - 2);
+    int i = (int)floor((tj - t_atm0) * inv_ts);  // the tile's interval up to rounding; s is exact w.r.t. the knots used
+    i = min(max(i, k0), k1 - 1);
     const double xi = P.t_atm[i];
     const R s = (R)((tj - xi) / (P.t_atm[i + 1] - xi));  // may leave [0, 1] by ~1e-6 (knot rounding) or at the ends
     const int li = i - wa;
@@ -162,20 +184,22 @@ __global__ void __launch_bounds__(SY_THREADS) synth_kernel(const __grid_constant
     const R h26 = spl[5 * li + 1];
     const R a2 = h26 * (a0 * a0 * a0 - a0), a3 = h26 * (s * s * s - s);
     R cef = (R)0, sef = (R)0;
-    if (units == MATM_UNITS_KRJ) {
+    if (krj) {
       cef = (R)P.bore_full[2 * j];
       sef = (R)P.bore_full[2 * j + 1];
     }
+    const YM<R>* p = ym + li;
+    R* o = out + dbase * n_t + j;
+#pragma unroll 4
     for (int dd = 0; dd < nd; dd++) {
-      const R* yy = y + dd * T::WP + li;
-      const R* mm = m + dd * T::WP + li;
-      R val = a0 * yy[0] + a1 * yy[1] + a2 * mm[0] + a3 * mm[1];
-      val *= dc_gain[dd];
-      if (units == MATM_UNITS_KRJ) {
+      const YM<R> q0 = p[dd * T::WP], q1 = p[dd * T::WP + 1];
+      R val = a0 * q0.y + a1 * q1.y + a2 * q0.m + a3 * q1.m;
+      if (krj) {
         const R sin_el = dc_u[dd] * sef + dc_w[dd] * cef;  // Im q of the rolled offsets at the full rate
-        val = val / cal_denominator<R>(P, dc_band[dd], sin_el);
+        const int ho = dc_hoff[dd];
+        val = r_div(val, cal_denominator<R>(P, sing, hcs + ho, hss + ho, sin_el, ie));
       }
-      out[(dbase + dd) * P.n_t + j] = val;
+      o[(int64_t)dd * n_t] = val;
     }
   }
 }
@@ -190,10 +214,13 @@ __global__ void __launch_bounds__(256) calibrate_kernel(const __grid_constant__ 
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= P.n_t) return;
   const R cef = (R)P.bore_full[2 * j], sef = (R)P.bore_full[2 * j + 1];
+  int ie = 0;
   for (int64_t d = blockIdx.y; d < n_det; d += gridDim.y) {
     const int64_t dg = det0 + d;
     const R sin_el = (R)P.det_full[2 * dg] * sef + (R)P.det_full[2 * dg + 1] * cef;
-    const R den = cal_denominator<R>(P, P.band_index[dg], sin_el);
+    const int ho = P.band_index[dg] * (P.nel - 1);
+    const R den = cal_denominator<R>(P, reinterpret_cast<const R*>(P.sinel_R), reinterpret_cast<const R*>(P.Hc_R) + ho,
+                                     reinterpret_cast<const R*>(P.Hs_R) + ho, sin_el, ie);
     const R x = in[d * P.n_t + j];
     out[d * P.n_t + j] = to_units == MATM_UNITS_KRJ ? x / den : x * den;
   }
@@ -246,7 +273,7 @@ extern "C" int matm_upsample_linear(matm_handle* h, const double* in_dev, int64_
 template <typename R>
 static size_t synth_smem(int n_layers) {
   using T = Tile<R>;
-  return (size_t)2 * DT * T::WP * sizeof(R) + 5 * T::W * sizeof(R) + T::W * sizeof(Knot<R>) +
+  return (size_t)DT * T::WP * sizeof(YM<R>) + 5 * T::W * sizeof(R) + T::W * sizeof(Knot<R>) +
          (size_t)n_layers * T::W * sizeof(LayerKnot<R>);
 }
 

@@ -101,8 +101,29 @@ def test_detector_shards_tile_the_full_tod(cuda):
     assert np.array_equal(np.concatenate(parts, axis=0), full)
 
 
-def test_philox_layers_have_matern_statistics(cuda):
-    """Production RNG: unit marginal variance and the Matern structure function across the extrusion axis."""
+def test_philox_normals_are_standard_normal(cuda):
+    """matm_fill_normal: moments, independence of neighbours, reproducibility, distinct subsequences."""
+    ctx = M.DeviceContext(0, "fp32")
+    n = 1 << 22
+    x = ctx.empty((n,), cuda.float64)
+    y = ctx.empty((n,), cuda.float64)
+    ctx.check(ctx.lib.matm_fill_normal(ctx.h, x.data_ptr(), n, 42, 0, ctx.stream_ptr()))
+    ctx.check(ctx.lib.matm_fill_normal(ctx.h, y.data_ptr(), n, 42, 1, ctx.stream_ptr()))
+    a, b = x.cpu().numpy(), y.cpu().numpy()
+    se = 1 / np.sqrt(n)
+    assert abs(a.mean()) < 5 * se and abs(a.var() - 1) < 5 * np.sqrt(2) * se
+    assert abs(np.mean(a**3)) < 5 * np.sqrt(15) * se and abs(np.mean(a**4) - 3) < 5 * np.sqrt(96) * se
+    assert abs(np.mean(a[1:] * a[:-1])) < 5 * se and abs(np.mean(a[::2] * a[1::2])) < 5 * np.sqrt(2) * se
+    assert abs(np.mean(a * b)) < 5 * se  # subsequences are independent
+    ctx.check(ctx.lib.matm_fill_normal(ctx.h, y.data_ptr(), n, 42, 0, ctx.stream_ptr()))
+    assert np.array_equal(a, y.cpu().numpy())
+
+
+def test_philox_layers_have_matern_structure_function(cuda):
+    """Production RNG: the second-order structure function D(r) = 2 (1 - C(r)) of the generated layers along the
+    extrusion axis follows the Matern covariance the process was built from.  The marginal
+    variance is NOT tested: the reference's propagator is close to a unit root, so the second moment of one realisation
+    scatters by factors of several in the reference itself."""
     case = small_case(n_det=32, duration=60.0, sample_rate=10.0, seed=3)
     np.random.seed(3)
     sim = M.Simulation(case["instrument"], case["plan"], case["site"], atmosphere="2d",
@@ -110,24 +131,23 @@ def test_philox_layers_have_matern_statistics(cuda):
     atm = sim.obs_list[0].atmosphere
     k = max(atm.processes)
     p = atm.processes[k]
-    var, sf = [], []
+    sf = []
     lags = np.array([1, 2, 4, 8])
-    for seed in range(64):
+    for seed in range(32):
         atm.seed = 1000 + seed
         atm.generate()
         v = p.values
-        var.append(np.mean(v**2))  # second moment about the true mean 0: the layer spans ~1 outer scale
         sf.append([np.mean((v[l:] - v[:-l]) ** 2) for l in lags])
-    cov = p.callback(lags * p.extrusion_res)
-    expected_sf = 2 * (1 - cov)
-    assert abs(np.mean(var) - 1) < 0.25
-    assert np.all(np.abs(np.mean(sf, axis=0) / expected_sf - 1) < 0.2)
-    # two different subsequences / seeds are different, the same seed reproduces
-    atm.seed = 5
+    expected_sf = 2 * (1 - p.callback(lags * p.extrusion_res))
+    assert np.all(np.abs(np.mean(sf, axis=0) / expected_sf - 1) < 0.2), (np.mean(sf, axis=0), expected_sf)
+    atm.seed = 5  # the same seed reproduces the same layers, a different one does not
     atm.generate()
     a = p.values.copy()
     atm.generate()
     assert np.array_equal(a, p.values)
+    atm.seed = 6
+    atm.generate()
+    assert not np.array_equal(a, p.values)
 
 
 def test_out_of_grid_raises_like_the_reference(cuda):
