@@ -185,13 +185,15 @@ static int launch_chain(matm_handle* h, const double* A, const int* esi, const i
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// The chain, latency-optimised (v2).  What bounds a step is not arithmetic but the round trips on its critical path,
-// so everything that is not the previous row is taken off that path:
-//   * A lives in REGISTERS: warp w of CTA c owns RW rows, lane l holds their entries for samples l, l+32, ...;
-//   * the last three rows (stencil offsets 1..3) live in a 4-slot shared-memory ring (row R -> slot R & 3), written
-//     by the owners of each element -- through distributed shared memory into every CTA of the cluster;
-//   * stencil rows further back (offsets >= 4) and the row's own B z term are read from L2 two steps ahead of their
-//     use (register pipeline of depth 2), so their latency never shows;
+// The chain, latency-optimised (v3).  A step is bounded by the round trips on its critical path, not by arithmetic,
+// so everything that is not "the previous row" is taken off that path and the rest is made short:
+//   * A lives in REGISTERS.  L lanes share a row (32 / L rows per warp): lane `sub` holds the entries of samples
+//     sub, sub + L, ...  ->  the cross-lane reduction is log2(L) shuffle stages instead of 5 per row;
+//   * the gather vector of step i is a contiguous shared-memory array G[i & 3][n_sample]: whoever produces a value
+//     writes it straight to where its consumers will read it -- the owner of (row i, column c) stores it into the
+//     G arrays of steps i-1, i-2, i-3 (stencil offsets 1..3) of EVERY CTA of the cluster through distributed
+//     shared memory, and the stencil rows further back (offsets >= 4) plus the row's own B z term are fetched
+//     from L2 two / three steps ahead of their use through a register pipeline, so their latency never shows;
 //   * one barrier per step: __syncthreads (1 CTA) or the hardware cluster barrier.
 // ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void cluster_barrier() {
@@ -204,147 +206,148 @@ __device__ __forceinline__ void st_dsmem_f64(double* local_ptr, int cta, double 
   asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(r), "d"(v) : "memory");
 }
 
-template <int RW, int M>
+template <int L, int MP>
 __global__ void __launch_bounds__(AR_THREADS, 1)
-    ar_chain_v2_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
+    ar_chain_v3_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
                        double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl) {
+  constexpr int RPW = 32 / L;  // rows per warp
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  double* hist = reinterpret_cast<double*>(smem_raw);  // [4][n_cs]
+  const int gs = L * MP;                                  // padded length of one gather vector
+  double* G = reinterpret_cast<double*>(smem_raw);        // [4][gs]
+  int* pos = reinterpret_cast<int*>(G + 4 * (size_t)gs);  // [3][n_cs]: position of column c among the samples of offset 1, 2, 3
   const int n_far = n_sample - n_near;
-  double* far = hist + 4 * (size_t)n_cs;               // [2][n_far]
   int cta = 0;
   if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
   const int rpc = (n_cs + cl - 1) / cl;
   const int row0 = cta * rpc;
   const int rows = max(0, min(n_cs, row0 + rpc) - row0);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rr = lane / L, sub = lane % L;
+  const int r = warp * RPW + rr;  // row within this CTA
+  const bool has_row = r < rows;
+  const int i_top = 2 * n_ext - 1;
 
-  // ---- per-thread constants: A entries and the stencil descriptors of this lane's samples ----
-  double a[RW][M];
-  int desc[M];  // near sample: (offset << 24) | column ; far sample: index among the far samples ; -1: none
+  // ---- set-up: A into registers, G zeroed, inverse stencil maps ----
+  double a[MP];
 #pragma unroll
-  for (int m = 0; m < M; m++) {
-    const int s = lane + 32 * m;
-    desc[m] = -1;
-    if (s < n_sample) desc[m] = s < n_near ? (((esi[s] + 1) << 24) | csi[s]) : (s - n_near);
-#pragma unroll
-    for (int rr = 0; rr < RW; rr++) {
-      const int r = warp * RW + rr;
-      a[rr][m] = (s < n_sample && r < rows) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
-    }
+  for (int m = 0; m < MP; m++) {
+    const int s = sub + L * m;
+    a[m] = (has_row && s < n_sample) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
   }
-  // far sample f handled by thread f (f < n_far <= AR_THREADS * 2): global offset relative to the row being computed
+  for (int e = tid; e < 4 * gs; e += AR_THREADS) G[e] = 0.0;
+  for (int e = tid; e < 3 * n_cs; e += AR_THREADS) pos[e] = -1;
+  __syncthreads();
+  for (int s = tid; s < n_near; s += AR_THREADS) pos[esi[s] * n_cs + csi[s]] = s;  // offset = esi + 1 in 1..3
+  // far sample f is fetched by thread f (n_far <= 2 * AR_THREADS): global offset relative to the row being computed
   int foff[2];
 #pragma unroll
   for (int q = 0; q < 2; q++) {
     const int f = tid + q * AR_THREADS;
     foff[q] = f < n_far ? (esi[n_near + f] + 1) * n_cs + csi[n_near + f] : -1;
   }
-
-  const int i_top = 2 * n_ext - 1;
-  // ---- prologue: ring <- rows i_top+1 .. i_top+3 (initial noise); far buffers and pipelines for the first steps ----
-  for (int e = tid; e < 3 * n_cs; e += AR_THREADS) {
-    const int R = i_top + 1 + e / n_cs, c = e % n_cs;
-    hist[(R & 3) * n_cs + c] = buffer[(size_t)R * n_cs + c];
+  __syncthreads();
+  // where this thread's row goes in the gather vectors of the next three steps (publisher lanes only)
+  int p1 = -1, p2 = -1, p3 = -1;
+  if (has_row && sub == 0) {
+    p1 = pos[row0 + r];
+    p2 = pos[n_cs + row0 + r];
+    p3 = pos[2 * n_cs + row0 + r];
+  }
+  // ---- prologue: the initial-noise rows i_top+1 .. i_top+3 feed steps i_top, i_top-1, i_top-2 ----
+  for (int e = tid; e < 3 * n_near; e += AR_THREADS) {
+    const int k = e / n_near, s = e % n_near;  // step i_top - k, near sample s
+    const int off = esi[s] + 1;
+    if (off > k && i_top - k >= 0)
+      G[((i_top - k) & 3) * gs + s] = buffer[(size_t)(i_top - k + off) * n_cs + csi[s]];
   }
 #pragma unroll
   for (int q = 0; q < 2; q++)
     if (foff[q] >= 0) {
-      const int f = tid + q * AR_THREADS;
-      far[(i_top & 1) * n_far + f] = buffer[(size_t)i_top * n_cs + foff[q]];
-      if (i_top >= 1) far[((i_top - 1) & 1) * n_far + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
+      const int f = n_near + tid + q * AR_THREADS;
+      G[(i_top & 3) * gs + f] = buffer[(size_t)i_top * n_cs + foff[q]];
+      if (i_top >= 1) G[((i_top - 1) & 3) * gs + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
     }
-  double far_p[2] = {0.0, 0.0};  // in flight: far values of step i - 2, loaded during step i
-  double bz_p1[RW], bz_p2[RW];   // B z of the rows of step i - 1 / i - 2
-#pragma unroll
-  for (int rr = 0; rr < RW; rr++) {
-    const int r = warp * RW + rr;
-    bz_p1[rr] = bz_p2[rr] = 0.0;
-    if (r < rows) {
-      bz_p1[rr] = buffer[(size_t)i_top * n_cs + row0 + r];
-      if (i_top >= 1) bz_p2[rr] = buffer[(size_t)(i_top - 1) * n_cs + row0 + r];
-    }
+  // Register pipelines, two sets each, used alternately by even / odd steps so that no register is copied while its
+  // load is still in flight (the loop below is unrolled by two for that reason):
+  //   far_s[i & 1]: issued at step i + 2 for step i - 1, landed in G at the start of step i, then re-issued
+  //   bz_s[i & 1] : issued at step i + 2 for step i, consumed when step i publishes, then re-issued for step i - 2
+  double far_s[2][2], bz_s[2];
+  far_s[0][0] = far_s[0][1] = far_s[1][0] = far_s[1][1] = 0.0;
+  bz_s[0] = bz_s[1] = 0.0;
+  if (has_row) {  // i_top is odd: set 1 serves step i_top, set 0 step i_top - 1
+    bz_s[1] = buffer[(size_t)i_top * n_cs + row0 + r];
+    bz_s[0] = buffer[(size_t)(i_top - 1) * n_cs + row0 + r];
   }
+#pragma unroll
+  for (int q = 0; q < 2; q++)  // far values of step i_top - 2 are landed by step i_top - 1 (set 0)
+    if (foff[q] >= 0 && i_top >= 2) far_s[0][q] = buffer[(size_t)(i_top - 2) * n_cs + foff[q]];
   __syncthreads();
   if (cl > 1) cluster_barrier();
 
-  for (int i = i_top; i >= 0; i--) {
-    // (1) issue the far / B z loads of step i - 2 (rows >= i + 2, complete since two barriers ago)
-    double far_n[2] = {0.0, 0.0}, bz_n[RW];
-    if (i >= 2) {
+  auto step = [&](const int i, double(&fs)[2], double& bz) {
+    // (1) land the far values of step i - 1 (in flight since step i + 2; step i_top has none: the prologue did it),
+    //     then re-issue the set for step i - 3 (rows >= i + 1, complete since the last barrier)
+    if (i < i_top && i >= 1) {
 #pragma unroll
       for (int q = 0; q < 2; q++)
-        if (foff[q] >= 0) far_n[q] = __ldcg(buffer + (size_t)(i - 2) * n_cs + foff[q]);
-#pragma unroll
-      for (int rr = 0; rr < RW; rr++) {
-        const int r = warp * RW + rr;
-        bz_n[rr] = r < rows ? __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r) : 0.0;
-      }
-    } else {
-#pragma unroll
-      for (int rr = 0; rr < RW; rr++) bz_n[rr] = 0.0;
+        if (foff[q] >= 0) G[((i - 1) & 3) * gs + n_near + tid + q * AR_THREADS] = fs[q];
     }
-    // (2) the dot products of this step, A from registers, x from shared memory
-    double acc[RW];
+    if (i >= 3) {
 #pragma unroll
-    for (int rr = 0; rr < RW; rr++) acc[rr] = 0.0;
-    const double* farp = far + (i & 1) * n_far;
-#pragma unroll
-    for (int m = 0; m < M; m++) {
-      const int d = desc[m];
-      double x = 0.0;
-      if (d >= 0) {
-        const int off = d >> 24;
-        x = off ? hist[((i + off) & 3) * n_cs + (d & 0xffffff)] : farp[d];
-      }
-#pragma unroll
-      for (int rr = 0; rr < RW; rr++) acc[rr] = fma(a[rr][m], x, acc[rr]);
+      for (int q = 0; q < 2; q++)
+        if (foff[q] >= 0) fs[q] = __ldcg(buffer + (size_t)(i - 3) * n_cs + foff[q]);
     }
+    // (2) the dot product of this thread's slice of its row: A from registers, x contiguous in shared memory
+    const double* g = G + (i & 3) * gs + sub;
+    double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
-    for (int rr = 0; rr < RW; rr++) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) acc[rr] += __shfl_xor_sync(0xffffffffu, acc[rr], o);
+    for (int m = 0; m < MP; m += 4) {
+      acc0 = fma(a[m], g[L * m], acc0);
+      if (m + 1 < MP) acc1 = fma(a[m + 1], g[L * (m + 1)], acc1);
+      if (m + 2 < MP) acc2 = fma(a[m + 2], g[L * (m + 2)], acc2);
+      if (m + 3 < MP) acc3 = fma(a[m + 3], g[L * (m + 3)], acc3);
     }
-    // (3) publish: lane rr of the warp writes row warp*RW+rr to the ring of every CTA and to global memory
+    double acc = (acc0 + acc1) + (acc2 + acc3);
 #pragma unroll
-    for (int rr = 0; rr < RW; rr++) {
-      const int r = warp * RW + rr;
-      if (lane == rr && r < rows) {
-        const double v = bz_p1[rr] + acc[rr];
-        double* slot = hist + (i & 3) * n_cs + row0 + r;
-        if (cl == 1) {
-          *slot = v;
-        } else {
-          for (int c = 0; c < cl; c++) st_dsmem_f64(slot, c, v);
+    for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    // (3) publish row r of step i: to global memory and into the gather vectors of steps i-1, i-2, i-3 of every CTA
+    if (has_row && sub == 0) {
+      const double v = bz + acc;
+      buffer[(size_t)i * n_cs + row0 + r] = v;
+      double* d1 = G + ((i - 1) & 3) * gs + p1;
+      double* d2 = G + ((i - 2) & 3) * gs + p2;
+      double* d3 = G + ((i - 3) & 3) * gs + p3;
+      if (cl == 1) {
+        if (p1 >= 0) *d1 = v;
+        if (p2 >= 0) *d2 = v;
+        if (p3 >= 0) *d3 = v;
+      } else {
+        for (int c = 0; c < cl; c++) {
+          if (p1 >= 0) st_dsmem_f64(d1, c, v);
+          if (p2 >= 0) st_dsmem_f64(d2, c, v);
+          if (p3 >= 0) st_dsmem_f64(d3, c, v);
         }
-        buffer[(size_t)i * n_cs + row0 + r] = v;
       }
     }
-    // (4) land the far values loaded one step ago (they belong to step i - 1) and rotate the pipelines
-    if (i >= 1) {
-#pragma unroll
-      for (int q = 0; q < 2; q++)
-        if (foff[q] >= 0 && i <= i_top - 1) far[((i - 1) & 1) * n_far + tid + q * AR_THREADS] = far_p[q];
-    }
-#pragma unroll
-    for (int q = 0; q < 2; q++) far_p[q] = far_n[q];
-#pragma unroll
-    for (int rr = 0; rr < RW; rr++) {
-      bz_p1[rr] = bz_p2[rr];
-      bz_p2[rr] = bz_n[rr];
-    }
+    // (4) re-issue the B z register for step i - 2
+    if (i >= 2 && has_row) bz = __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r);
     if (cl == 1)
       __syncthreads();
     else
       cluster_barrier();
+  };
+
+  for (int i = i_top; i >= 1; i -= 2) {  // i_top = 2 n_ext - 1 is odd
+    step(i, far_s[1], bz_s[1]);
+    step(i - 1, far_s[0], bz_s[0]);
   }
 }
 
-template <int RW, int M>
-static int launch_chain_v2(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
+template <int L, int MP>
+static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
                            int n_cs, int n_sample, int n_near, int cl, cudaStream_t stream) {
-  const size_t smem = (4 * (size_t)n_cs + 2 * (size_t)(n_sample - n_near)) * sizeof(double) + 16;
-  MATM_CUDA(h, cudaFuncSetAttribute(ar_chain_v2_kernel<RW, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16;
+  MATM_CUDA(h, cudaFuncSetAttribute(ar_chain_v3_kernel<L, MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cl, 1, 1);
   cfg.blockDim = dim3(AR_THREADS, 1, 1);
@@ -357,28 +360,30 @@ static int launch_chain_v2(matm_handle* h, const double* A, const int* esi, cons
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, ar_chain_v2_kernel<RW, M>, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl));
+  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, ar_chain_v3_kernel<L, MP>, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl));
   h->launches++;
   return MATM_OK;
 }
 
-// picks (cluster size, rows per warp, samples per lane) for the register-resident kernel; false if it does not fit
-static bool plan_v2(int n_cs, int n_sample, int* cl, int* rw, int* m) {
-  const int warps = AR_THREADS / 32;
-  int mm = (n_sample + 31) / 32;
-  mm = mm <= 4 ? 4 : mm <= 8 ? 8 : mm <= 12 ? 12 : mm <= 16 ? 16 : 0;
-  if (!mm) return false;
-  const int max_rw = mm <= 8 ? 4 : 2;  // RW * M <= 32 doubles of A per thread (no spills at 512 threads)
-  for (int c = 1; c <= 8; c *= 2) {
-    const int rpc = (n_cs + c - 1) / c;
-    int r = (rpc + warps - 1) / warps;
-    r = r <= 1 ? 1 : r <= 2 ? 2 : r <= 4 ? 4 : 0;
-    if (r && r <= max_rw) {
-      *cl = c;
-      *rw = r;
-      *m = mm;
-      return true;
-    }
+// picks (lanes per row, samples per lane, cluster size) for the register-resident kernel; false if it does not fit
+static bool plan_v3(int n_cs, int n_sample, int* L, int* MP, int* cl) {
+  static const int Ls[4] = {4, 8, 16, 32};
+  static const int MPs[4] = {16, 24, 32, 40};
+  for (int li = 0; li < 4; li++) {
+    if (n_sample > Ls[li] * 40) continue;
+    int mp = 0;
+    for (int mi = 0; mi < 4; mi++)
+      if (n_sample <= Ls[li] * MPs[mi]) {
+        mp = MPs[mi];
+        break;
+      }
+    const int rows_per_cta = (AR_THREADS / 32) * (32 / Ls[li]);
+    const int c = (n_cs + rows_per_cta - 1) / rows_per_cta;
+    if (c > 8) continue;  // a larger L only lowers rows_per_cta further
+    *L = Ls[li];
+    *MP = mp;
+    *cl = c;
+    return true;
   }
   return false;
 }
@@ -400,14 +405,15 @@ extern "C" int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sampl
 
   // register-resident kernel when the process fits it
   {
-    int cl2, rw, mm;
-    if (n_near >= 0 && n_near <= n_sample && n_ext >= 4 && (n_sample - n_near) <= 2 * AR_THREADS && plan_v2(n_cs, n_sample, &cl2, &rw, &mm)) {
-#define V2_CASE(RWV, MV) \
-  if (rw == RWV && mm == MV) \
-    return launch_chain_v2<RWV, MV>(h, A_dev, esi_dev, csi_dev, buffer_dev, n_ext, n_cs, n_sample, n_near, cl2, st);
-      V2_CASE(1, 4) V2_CASE(2, 4) V2_CASE(4, 4) V2_CASE(1, 8) V2_CASE(2, 8) V2_CASE(4, 8)
-      V2_CASE(1, 12) V2_CASE(2, 12) V2_CASE(1, 16) V2_CASE(2, 16)
-#undef V2_CASE
+    int L, mp, cl3;
+    if (n_near >= 0 && n_near <= n_sample && n_ext >= 4 && (n_sample - n_near) <= 2 * AR_THREADS &&
+        plan_v3(n_cs, n_sample, &L, &mp, &cl3)) {
+#define V3_CASE(LV, MV) \
+  if (L == LV && mp == MV) \
+    return launch_chain_v3<LV, MV>(h, A_dev, esi_dev, csi_dev, buffer_dev, n_ext, n_cs, n_sample, n_near, cl3, st);
+      V3_CASE(4, 16) V3_CASE(4, 24) V3_CASE(4, 32) V3_CASE(4, 40) V3_CASE(8, 16) V3_CASE(8, 24) V3_CASE(8, 32)
+      V3_CASE(8, 40) V3_CASE(16, 24) V3_CASE(16, 32) V3_CASE(16, 40) V3_CASE(32, 24) V3_CASE(32, 32) V3_CASE(32, 40)
+#undef V3_CASE
     }
   }
   // fallback (v1): smallest cluster whose per-CTA slice of A fits in shared memory; above 8 CTAs A streams from L2
