@@ -48,6 +48,8 @@ extern "C" int matm_destroy(matm_handle* h) {
   cudaFree(h->G2);
   cudaFree(h->H1);
   cudaFree(h->tabR);
+  cudaFree(h->calq);
+  cudaFree(h->calq_aux);
   cudaFree(h->flags);
   for (int i = 0; i < 2; i++) {
     cudaFree(h->stage_dev[i]);

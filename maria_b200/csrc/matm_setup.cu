@@ -356,6 +356,83 @@ __global__ void typed_tables_kernel(const double* __restrict__ pwv, const double
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// fp32 fast path of a14 (tod.py:106-142 -> band.py:235-255): the factor 1 / (factor k_B 1e12 H(el)) as a function of
+// t = sqrt(1 - sin el), tabulated as one quadratic per bin of width 1 / MATM_CAL_SCALE.  el(t) = pi/2 - 2 asin(t / sqrt 2)
+// is analytic on the whole range (no singularity at the zenith), H is the reference's piecewise-linear interpolant of
+// the folded transmission integral on the elevation grid, so inside a bin that holds no grid point the function is
+// smooth and a quadratic through three Chebyshev nodes is accurate to ~1e-10 relative.  A bin that holds exactly one
+// interior grid point gets two quadratics (entry + aux record, selected by comparing dt with the kink position); every
+// other case (outside the table, several grid points in one bin, table not covering T0 / pwv) is marked w = -1 and
+// evaluated by the generic code, which also raises the flags.
+// ---------------------------------------------------------------------------------------------------------
+static double cal_el_of_t(double t) { return M_PI / 2 - 2 * asin(fmin(t / M_SQRT2, 1.0)); }
+
+static void cal_fit(const double* el, const double* H, int iv, double tc, double half, float* c) {
+  // quadratic in dt (bin units, centre tc, dt in [-1/2, 1/2]) through the Chebyshev nodes of the bin, on the linear
+  // piece `iv` of H extended analytically
+  const double a = 0.4330127018922193;  // cos(pi / 6) / 2
+  double f[3];
+  for (int q = 0; q < 3; q++) {
+    const double t = tc + (q - 1) * a * 2 * half;
+    const double e = cal_el_of_t(t < 0 ? -t : t);  // el is even in t; the bin centred on t = 0 reaches t < 0
+    const double den = H[iv] + (H[iv + 1] - H[iv]) * (e - el[iv]) / (el[iv + 1] - el[iv]);
+    f[q] = 1.0 / den;
+  }
+  c[0] = (float)f[1];
+  c[1] = (float)((f[2] - f[0]) / (2 * a));
+  c[2] = (float)((f[2] + f[0] - 2 * f[1]) / (2 * a * a));
+}
+
+static void build_cal_table(const double* el, int nel, const double* H1, int n_bands, bool table_ok, int* n_per_band,
+                            std::vector<float>& tab, std::vector<float>& aux) {
+  const double scale = MATM_CAL_SCALE;
+  const int n = (int)ceil(M_SQRT2 * scale) + 3;  // t <= sqrt 2
+  *n_per_band = n;
+  tab.assign((size_t)n_bands * n * 4, 0.f);
+  aux.assign(4, 0.f);  // record 0 is unused (w = 0 means "plain bin")
+  const float qnan = nanf("");
+  for (int b = 0; b < n_bands; b++) {
+    const double* H = H1 + (size_t)b * nel;
+    for (int r = 0; r < n; r++) {
+      float* c = &tab[((size_t)b * n + r) * 4];
+      const double tc = r / scale, half = 0.5 / scale;
+      const double t_lo = fmax(tc - half, 0.0), t_hi = tc + half;
+      const double e_hi = cal_el_of_t(t_lo), e_lo = t_hi >= M_SQRT2 ? -M_PI / 2 : cal_el_of_t(t_hi);  // el falls as t grows
+      bool slow = !table_ok || e_lo < el[0] || e_hi > el[nel - 1];
+      int first = -1, count = 0;  // interior grid points inside the bin (closed, with a margin for the fp32 rounding of t)
+      const double margin = 1e-6;
+      for (int i = 1; i <= nel - 2; i++)
+        if (el[i] >= e_lo - margin && el[i] <= e_hi + margin) {
+          if (count == 0) first = i;
+          count++;
+        }
+      if (slow || count > 1) {
+        c[0] = c[1] = c[2] = qnan;
+        c[3] = -1.f;
+        continue;
+      }
+      if (count == 0) {
+        int iv = 0;
+        const double ec = cal_el_of_t(tc);
+        while (iv < nel - 2 && el[iv + 1] < ec) iv++;
+        cal_fit(el, H, iv, tc, half, c);
+        c[3] = 0.f;
+      } else {
+        // the kink el[first] sits at t_k; for t <= t_k (higher elevation) the piece is `first`, beyond it `first - 1`
+        const double t_k = sqrt(fmax(1.0 - sin(el[first]), 0.0));
+        cal_fit(el, H, first, tc, half, c);
+        c[3] = (float)(aux.size() / 4);
+        float a[4];
+        cal_fit(el, H, first - 1, tc, half, a);
+        a[3] = (float)((t_k - tc) * scale);
+        aux.insert(aux.end(), a, a + 4);
+      }
+    }
+  }
+}
+
 extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int nel, int nnu, const double* side_T_host,
                               const double* side_pwv_host, const double* side_el_host, const double* side_nu_host,
                               const double* emission_host, const double* opacity_host, const double* passband_host,
@@ -424,6 +501,18 @@ extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int
     P.Hs_R = base + esz * ((size_t)npwv + 2 * nel + (size_t)n_bands * npwv * nel + (size_t)n_bands * (nel - 1));
   }
   P.table_ok = (ok ? 1 : 0) | (okc ? 2 : 0);
+  if (h->dtype == MATM_F32) {
+    std::vector<double> H1h((size_t)n_bands * nel);
+    MATM_CUDA(h, cudaMemcpy(H1h.data(), h->H1, H1h.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    std::vector<float> tab, aux;
+    int n_per_band = 0;
+    build_cal_table(side_el_host, nel, H1h.data(), n_bands, okc, &n_per_band, tab, aux);
+    if ((rc = matm_upload(h, (float**)&h->calq, tab.data(), tab.size()))) return rc;
+    if ((rc = matm_upload(h, (float**)&h->calq_aux, aux.data(), aux.size()))) return rc;
+    P.calq = h->calq;
+    P.calq_aux = h->calq_aux;
+    P.calq_n = n_per_band;
+  }
   h->have_bands = true;
   return MATM_OK;
 }

@@ -1,6 +1,9 @@
 // The detector x time stages: a6/a7/a9 (line-of-sight sampling), a10 (linear upsample), and the fused
 // a6..a14 synthesis kernel (sampling -> emission lookup -> cubic not-a-knot upsample -> gain -> pW->K_RJ).
+#include <stdlib.h>
+
 #include "matm_synth.cuh"
+#include "matm_synth_f32.cuh"
 
 #define DT 32          // detectors per tile (one lane per detector in the atmosphere-rate phase)
 #define SY_THREADS 256
@@ -288,6 +291,15 @@ static int launch_synth(matm_handle* h, int64_t det0, int64_t n_det, void* out_d
     size_t smem = synth_smem<double>(P.n_layers);
     MATM_CUDA(h, cudaFuncSetAttribute(synth_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     synth_kernel<double><<<(unsigned)blocks, SY_THREADS, smem, st>>>(P, det0, n_det, (double*)out_dev, units, apply_gain);
+  } else if (getenv("MATM_SYNTH_GENERIC") == nullptr) {
+    // production float kernel (matm_synth_f32.cuh)
+    const int n_ttiles = (P.n_t_atm - 1 + F32_KT - 1) / F32_KT;
+    const int64_t blocks = ((n_det + F32_DT - 1) / F32_DT) * n_ttiles;
+    if (blocks > INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize: too many tiles; split the detector range");
+    if (P.n_t * (int64_t)F32_DT > (int64_t)INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize: n_t too large for one launch; split in time");
+    size_t smem = synth_f32_smem(P.n_layers);
+    MATM_CUDA(h, cudaFuncSetAttribute(synth_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    synth_f32_kernel<<<(unsigned)blocks, F32_THREADS, smem, st>>>(P, det0, n_det, (float*)out_dev, units, apply_gain);
   } else {
     const int n_ttiles = (P.n_t_atm - 1 + Tile<float>::KT - 1) / Tile<float>::KT;
     const int64_t blocks = ((n_det + DT - 1) / DT) * n_ttiles;

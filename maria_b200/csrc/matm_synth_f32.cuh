@@ -1,0 +1,343 @@
+// The production (float) instance of the fused synthesis kernel a6..a14, written for instruction count: the kernel is
+// issue-bound, not HBM-bound (ncu: ~140 thread-instructions per output sample in the generic template), so every
+// per-output-sample operation is stripped to the minimum and done on two detectors at once with the packed
+// fma.rn.f32x2 / mul / add instructions of sm_100.
+//
+//   phase 1  loading [pW] at the window's knots; lane = detector, warps stride over knots          (per knot)
+//   phase 2  not-a-knot cubic spline second derivatives by the windowed Thomas sweep               (per knot)
+//   phase 3  spline evaluation + pW -> K_RJ at the full-rate samples; thread = sample, loop over   (per sample)
+//            detector PAIRS: 2 LDS.128 + 4 packed FMAs for the spline, and the calibration factor from the
+//            t = sqrt(1 - sin el) table of matm_setup.cu (no asin, no search, no divide).
+#pragma once
+#include "matm_synth.cuh"
+
+#define F32_DT 32
+#define F32_THREADS 256
+#define F32_KT 128
+#define F32_HALO 12
+#define F32_W (F32_KT + 1 + 2 * F32_HALO)
+#define F32_NP (F32_DT / 2)  // detector pairs per tile
+
+struct LayerF {  // per-layer constants, two 16-byte shared-memory loads + the pointer
+  float D0, D1, D2, D3;
+  float rms;
+  int ne1, nc1, n_cs;  // n_ext - 1, n_cs - 1, n_cs
+  const float* data;
+  int pad[2];
+};
+
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ float fast_sqrt(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// asin on [-1, 1]: pi/2 - sqrt(1 - |x|) P7(|x|)  (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 rad)
+__device__ __forceinline__ float fast_asin(float x) {
+  const float a = fabsf(x);
+  float p = -0.0012624911f;
+  p = fmaf(p, a, 0.0066700901f);
+  p = fmaf(p, a, -0.0170881256f);
+  p = fmaf(p, a, 0.0308918810f);
+  p = fmaf(p, a, -0.0501743046f);
+  p = fmaf(p, a, 0.0889789874f);
+  p = fmaf(p, a, -0.2145988016f);
+  p = fmaf(p, a, 1.5707963050f);
+  const float r = fmaf(-fast_sqrt(fmaxf(1.0f - a, 0.0f)), p, 1.5707963268f);
+  return copysignf(r, x);
+}
+
+// Exact (searching) evaluation of the calibration factor for the rare bins the table marks w < 0; raises the flag.
+__device__ __noinline__ float cal_factor_slow(const SynthParams& P, int band, float sin_el) {
+  int ie = 0;
+  const int ho = band * (P.nel - 1);
+  const float den = cal_denominator<float>(P, reinterpret_cast<const float*>(P.sinel_R),
+                                           reinterpret_cast<const float*>(P.Hc_R) + ho,
+                                           reinterpret_cast<const float*>(P.Hs_R) + ho, sin_el, ie);
+  return 1.0f / den;
+}
+
+__global__ void __launch_bounds__(F32_THREADS, 3)
+    synth_f32_kernel(const __grid_constant__ SynthParams P, int64_t det0, int64_t n_det, float* __restrict__ out, int units,
+                     int apply_gain) {
+  extern __shared__ __align__(16) unsigned char dyn[];
+  float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_d0, y_d1, m_d0, m_d1}
+  float* ymf = reinterpret_cast<float*>(dyn);
+  float* spl = reinterpret_cast<float*>(ym4 + F32_W * F32_NP);       // [W][5]
+  Knot<float>* knots = reinterpret_cast<Knot<float>*>(spl + 5 * F32_W + 3);  // 16-byte aligned: 5 W + 3 = 768
+  LayerKnot<float>* lk = reinterpret_cast<LayerKnot<float>*>(knots + F32_W);  // [n_layers][W]
+  __shared__ __align__(16) LayerF ls[MATM_MAX_LAYERS];
+  __shared__ float4 dc_uw[F32_NP];  // {u_d0, u_d1, w_d0, w_d1} of the rolled offsets
+  __shared__ int2 dc_tab[F32_NP];   // calibration-table base of each detector's band, minus the rounding magic
+  __shared__ float dc_gain[F32_DT];
+  __shared__ int dc_band[F32_DT];
+
+  const int n = P.n_t_atm;
+  const int n_int = n - 1;
+  const int n_layers = P.n_layers;
+  const int n_ttiles = (n_int + F32_KT - 1) / F32_KT;
+  const int64_t dtile = blockIdx.x / n_ttiles;
+  const int ttile = blockIdx.x % n_ttiles;
+  const int k0 = ttile * F32_KT, k1 = min(k0 + F32_KT, n_int);
+  const int wa = max(0, k0 - F32_HALO), wb = min(n - 1, k1 + F32_HALO);
+  const int Wn = wb - wa + 1;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t dbase = dtile * F32_DT;
+  const int nd = (int)min((int64_t)F32_DT, n_det - dbase);
+  constexpr int MAGIC_BITS = 0x4B400000;  // bits of 1.5 * 2^23
+
+  // ---- stage the window: knots, per-layer boresight cells, per-layer constants, spline system, detector constants ----
+  for (int k = tid; k < Wn; k += F32_THREADS) {
+    const double* b = P.bore_atm + 4 * (size_t)(wa + k);
+    Knot<float> o;
+    o.ce = (float)b[0];
+    o.se = (float)b[1];
+    o.ca = (float)b[2];
+    o.sa = (float)b[3];
+    knots[k] = o;
+  }
+  for (int e = tid; e < n_layers * Wn; e += F32_THREADS) {
+    const int l = e / Wn, k = e % Wn;
+    const double* b = P.layers[l].base + 2 * (size_t)(wa + k);
+    const double cx = b[0], cy = b[1];
+    const double flx = fmin(fmax(floor(cx), -1.0e9), 1.0e9), fly = fmin(fmax(floor(cy), -1.0e9), 1.0e9);
+    LayerKnot<float> o;
+    o.ix = (int)flx;
+    o.iy = (int)fly;
+    o.fx = (float)(cx - flx);
+    o.fy = (float)(cy - fly);
+    lk[l * F32_W + k] = o;
+  }
+  if (tid < n_layers) {
+    const LayerDev& L = P.layers[tid];
+    LayerF o;
+    o.D0 = (float)L.D[0];
+    o.D1 = (float)L.D[1];
+    o.D2 = (float)L.D[2];
+    o.D3 = (float)L.D[3];
+    o.rms = (float)L.pwv_rms;
+    o.ne1 = L.n_ext - 1;
+    o.nc1 = L.n_cs - 1;
+    o.n_cs = L.n_cs;
+    o.data = reinterpret_cast<const float*>(L.data);
+    o.pad[0] = o.pad[1] = 0;
+    ls[tid] = o;
+  }
+  if (tid < F32_DT) {
+    const int dd = tid;
+    float u = 0.f, w = 1.f, g = 0.f;
+    int band = 0;
+    if (dd < nd) {
+      const int64_t d = det0 + dbase + dd;
+      u = (float)P.det_full[2 * d];
+      w = (float)P.det_full[2 * d + 1];
+      g = apply_gain ? (float)P.gain[d] : 1.f;
+      band = P.band_index[d];
+    }
+    dc_gain[dd] = g;
+    dc_band[dd] = band;
+    float* uw = reinterpret_cast<float*>(dc_uw);
+    uw[(dd >> 1) * 4 + (dd & 1)] = u;
+    uw[(dd >> 1) * 4 + 2 + (dd & 1)] = w;
+    reinterpret_cast<int*>(dc_tab)[dd] = band * P.calq_n - MAGIC_BITS;
+  }
+  for (int e = tid; e < 5 * Wn; e += F32_THREADS) spl[e] = (float)P.spl[5 * (size_t)wa + e];
+  __syncthreads();
+
+  // ---- phase 1: loading [pW] at the window's knots ----
+  {
+    const int64_t d = det0 + dbase + min(lane, nd - 1);  // idle lanes of a partial tile shadow the last detector
+    const double* da = P.det_atm + 4 * d;
+    const float u = (float)da[0], Y = (float)da[1], wm1 = (float)da[2];
+    const int band = P.band_index[d];
+    const float mu = (float)P.mueller00[d];
+    const float pwv0 = (float)P.pwv0;
+    int ip = 0, ie = 0;
+    float* yrow = ymf + (lane >> 1) * 4 + (lane & 1);
+    for (int k = warp; k < Wn; k += F32_THREADS / 32) {
+      const Knot<float> kc = knots[k];
+      // direction of the detector minus direction of the boresight, horizon frame (coords/transforms.py:10-29)
+      const float dX = u * kc.ce - wm1 * kc.se;
+      const float dZ = u * kc.se + wm1 * kc.ce;
+      const float dNx = dX * kc.ca - Y * kc.sa;
+      const float dNy = dX * kc.sa + Y * kc.ca;
+      const float Nbx = -kc.se * kc.ca, Nby = -kc.se * kc.sa, Nbz = kc.ce;
+      const float Nz = Nbz + dZ;  // = sin(el) of the detector
+      const float inv = fast_rcp(Nbz * Nz);
+      const float dppx = (dNx * Nbz - Nbx * dZ) * inv;  // pp_d - pp_b (coordinates.py:333-349)
+      const float dppy = (dNy * Nbz - Nby * dZ) * inv;
+      float acc = 0.f;
+      bool bad = !(dppx == dppx) || !(dppy == dppy);
+      const LayerKnot<float>* lkk = lk + k;
+#pragma unroll 2
+      for (int l = 0; l < n_layers; l++) {
+        const float4 Dm = *reinterpret_cast<const float4*>(&ls[l].D0);
+        const int4 Ln = *reinterpret_cast<const int4*>(&ls[l].rms);
+        const float* data = ls[l].data;
+        const LayerKnot<float> b = lkk[l * F32_W];
+        const float fx = fmaf(Dm.x, dppx, fmaf(Dm.y, dppy, b.fx));
+        const float fy = fmaf(Dm.z, dppx, fmaf(Dm.w, dppy, b.fy));
+        const float flx = floorf(fx), fly = floorf(fy);
+        int ix = b.ix + (int)flx, iy = b.iy + (int)fly;
+        float wx = fx - flx, wy = fy - fly;
+        if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
+          // rare: exactly on the last grid line is inside (RGI clips the index to n - 2); anything else is outside
+          if (ix == Ln.y && wx == 0.f) {
+            ix--;
+            wx = 1.f;
+          }
+          if (iy == Ln.z && wy == 0.f) {
+            iy--;
+            wy = 1.f;
+          }
+          if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
+            record_out_of_grid(P.flags, l, d, wa + k);  // atmosphere.py:368-369
+            bad = true;
+            ix = iy = 0;
+          }
+        }
+        const float* v = data + (ix * Ln.w + iy);
+        const float v00 = __ldg(v), v01 = __ldg(v + 1), v10 = __ldg(v + Ln.w), v11 = __ldg(v + Ln.w + 1);
+        const float a = fmaf(wy, v01 - v00, v00), bb = fmaf(wy, v11 - v10, v10);
+        acc = fmaf(__int_as_float(Ln.x), fmaf(wx, bb - a, a), acc);
+      }
+      if (bad) {
+        if (!(dppx == dppx) || !(dppy == dppy)) record_out_of_grid(P.flags, 0, d, wa + k);
+        acc = r_nan<float>();
+      }
+      yrow[k * (F32_NP * 4)] = loading_pW<float>(P, band, mu, pwv0 + acc, Nz, ip, ie);
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 2: spline second derivatives (see the generic kernel for the derivation); warp 0, lane = detector ----
+  if (warp == 0) {
+    float* row = ymf + (lane >> 1) * 4 + (lane & 1);
+    constexpr int RS = F32_NP * 4;  // stride between knots, in floats
+    auto yv = [&](int k) { return row[k * RS]; };
+    auto mref = [&](int k) -> float& { return row[k * RS + 2]; };
+    auto invh = [&](int k) { return spl[5 * k + 0]; };
+    auto rhs = [&](int k) { return 6.f * ((yv(k + 1) - yv(k)) * invh(k) - (yv(k) - yv(k - 1)) * invh(k - 1)); };
+    auto guess = [&](int k) { return rhs(k) / (3.f * (1.f / invh(k - 1) + 1.f / invh(k))); };
+    const int lo = 1, hi = Wn - 2;
+    float dp = (wa == 0) ? rhs(lo) * spl[5 * lo + 2] : guess(lo) * (1.f + spl[5 * lo + 4]);
+    mref(lo) = dp;
+    for (int k = lo + 1; k <= hi; k++) {
+      dp = rhs(k) * spl[5 * k + 2] - spl[5 * k + 3] * dp;
+      mref(k) = dp;
+    }
+    if (wb != n - 1) mref(hi) -= spl[5 * hi + 4] * guess(hi);
+    for (int k = hi - 1; k >= lo; k--) mref(k) -= spl[5 * k + 4] * mref(k + 1);
+    mref(0) = (wa == 0) ? mref(1) - (invh(1) / invh(0)) * (mref(2) - mref(1)) : mref(1);
+    mref(Wn - 1) = (wb == n - 1) ? mref(Wn - 2) + (invh(Wn - 3) / invh(Wn - 2)) * (mref(Wn - 2) - mref(Wn - 3)) : mref(Wn - 2);
+    const float g = dc_gain[lane];  // the spline is linear in the data: fold the detector gain in here
+    for (int k = 0; k < Wn; k++) {
+      row[k * RS] *= g;
+      row[k * RS + 2] *= g;
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 3: evaluate at the full-rate samples of the tile; thread = sample, loop over detector pairs ----
+  const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
+  const double t_atm0 = P.t_atm0, inv_ts = 1.0 / P.timestep;
+  const float inv_ts_f = (float)inv_ts;
+  const int n_t32 = (int)P.n_t;  // host guarantees 32 * n_t < 2^31
+  const bool krj = units == MATM_UNITS_KRJ;
+  const int npairs = nd >> 1;
+  const float4* __restrict__ calq = P.calq;
+  const float2 scale2 = f2(MATM_CAL_SCALE, MATM_CAL_SCALE), magic2 = f2(12582912.f, 12582912.f);
+  for (int64_t j = j0 + tid; j < j1; j += F32_THREADS) {
+    const double tj = P.t_full[j];
+    int i = (int)floor((tj - t_atm0) * inv_ts);
+    i = min(max(i, k0), k1 - 1);
+    const int li = i - wa;
+    const float s = (float)(tj - P.t_atm[i]) * (spl[5 * li] * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
+    const float a0 = 1.f - s;
+    const float h26 = spl[5 * li + 1];
+    const float a2 = h26 * (a0 * a0 * a0 - a0), a3 = h26 * (s * s * s - s);
+    const float2 A0 = f2(a0, a0), A1 = f2(s, s), A2 = f2(a2, a2), A3 = f2(a3, a3);
+    float2 SE = f2(0.f, 0.f), CE = SE;
+    if (krj) {
+      const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
+      CE = f2((float)bf.x, (float)bf.x);
+      SE = f2((float)bf.y, (float)bf.y);
+    }
+    const float4* yk = ym4 + li * F32_NP;
+    float* o0 = out + dbase * (int64_t)n_t32 + j;
+    float* o1 = o0 + n_t32;
+    const int64_t ostride = 2 * (int64_t)n_t32;
+#pragma unroll 4
+    for (int p = 0; p < npairs; p++) {
+      const float4 q0 = yk[p], q1 = yk[F32_NP + p];
+      float2 v = __fmul2_rn(A0, f2(q0.x, q0.y));
+      v = __ffma2_rn(A1, f2(q1.x, q1.y), v);
+      v = __ffma2_rn(A2, f2(q0.z, q0.w), v);
+      v = __ffma2_rn(A3, f2(q1.z, q1.w), v);
+      if (krj) {
+        const float4 uw = dc_uw[p];
+        const int2 tb = dc_tab[p];
+        const float2 sn = __ffma2_rn(f2(uw.x, uw.y), SE, __fmul2_rn(f2(uw.z, uw.w), CE));  // sin(el), rolled offsets
+        const float2 t = f2(fast_sqrt(fmaxf(1.f - sn.x, 0.f)), fast_sqrt(fmaxf(1.f - sn.y, 0.f)));
+        const float2 x = __ffma2_rn(t, scale2, magic2);      // round(t * scale) in the low mantissa bits
+        const float2 r = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
+        const float2 dt = __ffma2_rn(t, scale2, f2(-r.x, -r.y));
+        const float4 c0 = __ldg(calq + (__float_as_int(x.x) + tb.x));
+        const float4 c1 = __ldg(calq + (__float_as_int(x.y) + tb.y));
+        float2 f;  // scalar on purpose: the operands sit in the registers of two different loads
+        f.x = fmaf(fmaf(c0.z, dt.x, c0.y), dt.x, c0.x);
+        f.y = fmaf(fmaf(c1.z, dt.y, c1.y), dt.y, c1.x);
+        if (c0.w != 0.f || c1.w != 0.f) {  // a bin with a grid point of the elevation table, or outside the table
+          if (c0.w > 0.f) {
+            const float4 a = __ldg(P.calq_aux + (int)c0.w);
+            if (dt.x > a.w) f.x = fmaf(fmaf(a.z, dt.x, a.y), dt.x, a.x);
+          } else if (c0.w < 0.f) {
+            f.x = cal_factor_slow(P, dc_band[2 * p], sn.x);
+          }
+          if (c1.w > 0.f) {
+            const float4 a = __ldg(P.calq_aux + (int)c1.w);
+            if (dt.y > a.w) f.y = fmaf(fmaf(a.z, dt.y, a.y), dt.y, a.x);
+          } else if (c1.w < 0.f) {
+            f.y = cal_factor_slow(P, dc_band[2 * p + 1], sn.y);
+          }
+        }
+        v = __fmul2_rn(v, f);
+      }
+      *o0 = v.x;
+      *o1 = v.y;
+      o0 += ostride;
+      o1 += ostride;
+    }
+    if (nd & 1) {  // odd tail detector of a partial tile
+      const int p = npairs;
+      const float4 q0 = yk[p], q1 = yk[F32_NP + p];
+      float v = fmaf(a3, q1.z, fmaf(a2, q0.z, fmaf(s, q1.x, a0 * q0.x)));
+      if (krj) {  // the same arithmetic as the paired path, so that any detector sharding gives identical bits
+        const float sn = fmaf(dc_uw[p].x, SE.x, dc_uw[p].z * CE.x);
+        const float t = fast_sqrt(fmaxf(1.f - sn, 0.f));
+        const float x = fmaf(t, MATM_CAL_SCALE, 12582912.f);
+        const float dt = fmaf(t, MATM_CAL_SCALE, -(x - 12582912.f));
+        const float4 c0 = __ldg(calq + (__float_as_int(x) + dc_tab[p].x));
+        float f = fmaf(fmaf(c0.z, dt, c0.y), dt, c0.x);
+        if (c0.w > 0.f) {
+          const float4 a = __ldg(P.calq_aux + (int)c0.w);
+          if (dt > a.w) f = fmaf(fmaf(a.z, dt, a.y), dt, a.x);
+        } else if (c0.w < 0.f) {
+          f = cal_factor_slow(P, dc_band[2 * p], sn);
+        }
+        v *= f;
+      }
+      *o0 = v;
+    }
+  }
+}
+
+static size_t synth_f32_smem(int n_layers) {
+  return (size_t)F32_W * F32_NP * sizeof(float4) + (5 * F32_W + 3) * sizeof(float) + F32_W * sizeof(Knot<float>) +
+         (size_t)n_layers * F32_W * sizeof(LayerKnot<float>);
+}
