@@ -34,7 +34,7 @@ def build(force=False, verbose=False):
     if not force and not is_stale():
         return LIB
     nvcc = _nvcc()
-    flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"]
+    flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"] + os.environ.get("MATM_NVCC_FLAGS", "").split()
     objs = []
     log = []
     for s in SOURCES:

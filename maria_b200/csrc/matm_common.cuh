@@ -5,7 +5,9 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <map>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/maria_atm.h"
@@ -84,6 +86,9 @@ struct matm_handle {
   double *side_pwv = nullptr, *side_el = nullptr, *G2 = nullptr, *H1 = nullptr;
   void* tabR = nullptr;  // one allocation holding the R-typed tables
   float4 *calq = nullptr, *calq_aux = nullptr;
+  // processing order of the detectors of a requested range (spatially coherent tiles; matm_detector_order)
+  std::vector<float> det_xy_host;  // (n_det, 2) the atmosphere's offsets, kept for the ordering
+  std::map<std::pair<int64_t, int64_t>, int32_t*> det_order;
   int* flags = nullptr;
   std::vector<double> az_atm_host, el_atm_host;
   // e2e staging
@@ -130,6 +135,11 @@ static inline int matm_upload(matm_handle* h, T** dst, const T* src_host, size_t
   if (src_host) MATM_CUDA(h, cudaMemcpy(*dst, src_host, n * sizeof(T), cudaMemcpyHostToDevice));
   return MATM_OK;
 }
+
+// Device array of n_det absolute detector indices: the order in which the detectors of [det0, det0 + n_det) are
+// processed.  Consecutive entries are neighbours in the focal plane (Morton order of the offsets), so that the 32
+// detectors of a warp sample the same few cells of every layer whatever order the caller's array is in.
+int matm_detector_order(matm_handle* h, int64_t det0, int64_t n_det, const int32_t** order_dev);
 
 static inline int matm_set_device(matm_handle* h) {
   MATM_CUDA(h, cudaSetDevice(h->device));

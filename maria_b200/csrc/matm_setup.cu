@@ -1,5 +1,7 @@
 // Set-up entry points: scan, layers, detectors, band tables.  Small host arrays are uploaded and the derived
 // per-time / per-detector / per-band constants are evaluated on the device in float64.
+#include <algorithm>
+
 #include "matm_common.cuh"
 
 #define K_B 1.380649e-23
@@ -261,6 +263,10 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   MATM_CUDA(h, cudaDeviceSynchronize());
   cudaFree(oa);
   cudaFree(of);
+  h->det_xy_host.resize((size_t)n_det * 2);
+  for (size_t i = 0; i < (size_t)n_det * 2; i++) h->det_xy_host[i] = (float)offsets_atm_host[i];
+  for (auto& kv : h->det_order) cudaFree(kv.second);
+  h->det_order.clear();
   SynthParams& P = h->P;
   P.n_det = n_det;
   P.det_atm = h->det_atm;
@@ -269,6 +275,50 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   P.mueller00 = h->mueller00;
   P.gain = h->gain;
   h->have_dets = true;
+  return MATM_OK;
+}
+
+static inline uint32_t spread_bits16(uint32_t v) {  // 16 bits -> every other bit of 32
+  v = (v | (v << 8)) & 0x00FF00FFu;
+  v = (v | (v << 4)) & 0x0F0F0F0Fu;
+  v = (v | (v << 2)) & 0x33333333u;
+  v = (v | (v << 1)) & 0x55555555u;
+  return v;
+}
+
+int matm_detector_order(matm_handle* h, int64_t det0, int64_t n_det, const int32_t** order_dev) {
+  const auto key = std::make_pair(det0, n_det);
+  auto it = h->det_order.find(key);
+  if (it != h->det_order.end()) {
+    *order_dev = it->second;
+    return MATM_OK;
+  }
+  if (h->det_order.size() >= 256) {  // bounded cache (chunked delivery asks for a handful of ranges)
+    for (auto& kv : h->det_order) cudaFree(kv.second);
+    h->det_order.clear();
+  }
+  const float* xy = h->det_xy_host.data() + 2 * (size_t)det0;
+  float lo[2] = {xy[0], xy[1]}, hi[2] = {xy[0], xy[1]};
+  for (int64_t i = 0; i < n_det; i++)
+    for (int a = 0; a < 2; a++) {
+      lo[a] = fminf(lo[a], xy[2 * i + a]);
+      hi[a] = fmaxf(hi[a], xy[2 * i + a]);
+    }
+  const float span = fmaxf(fmaxf(hi[0] - lo[0], hi[1] - lo[1]), 1e-30f);
+  std::vector<std::pair<uint32_t, int32_t>> keyed((size_t)n_det);
+  for (int64_t i = 0; i < n_det; i++) {
+    const uint32_t qx = (uint32_t)fminf(65535.f, (xy[2 * i] - lo[0]) / span * 65535.f);
+    const uint32_t qy = (uint32_t)fminf(65535.f, (xy[2 * i + 1] - lo[1]) / span * 65535.f);
+    keyed[(size_t)i] = std::make_pair(spread_bits16(qx) | (spread_bits16(qy) << 1), (int32_t)(det0 + i));
+  }
+  std::sort(keyed.begin(), keyed.end());  // ties (co-located detectors of different bands) stay in index order
+  std::vector<int32_t> order((size_t)n_det);
+  for (int64_t i = 0; i < n_det; i++) order[(size_t)i] = keyed[(size_t)i].second;
+  int32_t* dev = nullptr;
+  MATM_CUDA(h, cudaMalloc((void**)&dev, (size_t)n_det * sizeof(int32_t)));
+  MATM_CUDA(h, cudaMemcpy(dev, order.data(), (size_t)n_det * sizeof(int32_t), cudaMemcpyHostToDevice));
+  h->det_order[key] = dev;
+  *order_dev = dev;
   return MATM_OK;
 }
 

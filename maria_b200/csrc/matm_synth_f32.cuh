@@ -13,10 +13,21 @@
 
 #define F32_DT 32
 #define F32_THREADS 256
-#define F32_KT 128
-#define F32_HALO 12
+#ifndef F32_KT
+#define F32_KT 128   // spline intervals per tile
+#endif
+#ifndef F32_HALO
+#define F32_HALO 12  // extra knots each side; the error of the artificial boundary decays as (2 - sqrt 3)^HALO
+#endif
+#ifndef F32_MINB
+#define F32_MINB 3   // CTAs per SM the register allocation is held to
+#endif
 #define F32_W (F32_KT + 1 + 2 * F32_HALO)
 #define F32_NP (F32_DT / 2)  // detector pairs per tile
+#define F32_SPLN ((5 * F32_W + 3) & ~3)  // floats reserved for the spline system (keeps what follows 16-byte aligned)
+#ifndef F32_G
+#define F32_G 4  // knots per thread and iteration in phase 1
+#endif
 
 struct LayerF {  // per-layer constants, two 16-byte shared-memory loads + the pointer
   float D0, D1, D2, D3;
@@ -62,20 +73,21 @@ __device__ __noinline__ float cal_factor_slow(const SynthParams& P, int band, fl
   return 1.0f / den;
 }
 
-__global__ void __launch_bounds__(F32_THREADS, 3)
-    synth_f32_kernel(const __grid_constant__ SynthParams P, int64_t det0, int64_t n_det, float* __restrict__ out, int units,
-                     int apply_gain) {
+__global__ void __launch_bounds__(F32_THREADS, F32_MINB)
+    synth_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order, int64_t det0, int64_t n_det,
+                     float* __restrict__ out, int units, int apply_gain) {
   extern __shared__ __align__(16) unsigned char dyn[];
   float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_d0, y_d1, m_d0, m_d1}
   float* ymf = reinterpret_cast<float*>(dyn);
   float* spl = reinterpret_cast<float*>(ym4 + F32_W * F32_NP);       // [W][5]
-  Knot<float>* knots = reinterpret_cast<Knot<float>*>(spl + 5 * F32_W + 3);  // 16-byte aligned: 5 W + 3 = 768
+  Knot<float>* knots = reinterpret_cast<Knot<float>*>(spl + F32_SPLN);
   LayerKnot<float>* lk = reinterpret_cast<LayerKnot<float>*>(knots + F32_W);  // [n_layers][W]
   __shared__ __align__(16) LayerF ls[MATM_MAX_LAYERS];
   __shared__ float4 dc_uw[F32_NP];  // {u_d0, u_d1, w_d0, w_d1} of the rolled offsets
   __shared__ int2 dc_tab[F32_NP];   // calibration-table base of each detector's band, minus the rounding magic
   __shared__ float dc_gain[F32_DT];
   __shared__ int dc_band[F32_DT];
+  __shared__ __align__(16) long long dc_row[F32_DT];  // element offset of each detector's output row
 
   const int n = P.n_t_atm;
   const int n_int = n - 1;
@@ -132,8 +144,10 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
     const int dd = tid;
     float u = 0.f, w = 1.f, g = 0.f;
     int band = 0;
+    long long row = 0;
     if (dd < nd) {
-      const int64_t d = det0 + dbase + dd;
+      const int64_t d = order[dbase + dd];  // absolute detector index of this slot
+      row = (d - det0) * P.n_t;
       u = (float)P.det_full[2 * d];
       w = (float)P.det_full[2 * d + 1];
       g = apply_gain ? (float)P.gain[d] : 1.f;
@@ -141,6 +155,7 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
     }
     dc_gain[dd] = g;
     dc_band[dd] = band;
+    dc_row[dd] = row;
     float* uw = reinterpret_cast<float*>(dc_uw);
     uw[(dd >> 1) * 4 + (dd & 1)] = u;
     uw[(dd >> 1) * 4 + 2 + (dd & 1)] = w;
@@ -150,8 +165,11 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
   __syncthreads();
 
   // ---- phase 1: loading [pW] at the window's knots ----
+  // Each thread works on F32_G knots at once: F32_G independent gather chains per layer keep 4 F32_G loads in flight
+  // (the layers live in L2; a dependent chain per knot leaves the SM waiting on that latency), and the per-layer
+  // constants are fetched once per group.
   {
-    const int64_t d = det0 + dbase + min(lane, nd - 1);  // idle lanes of a partial tile shadow the last detector
+    const int64_t d = order[dbase + min(lane, nd - 1)];  // idle lanes of a partial tile shadow the last detector
     const double* da = P.det_atm + 4 * d;
     const float u = (float)da[0], Y = (float)da[1], wm1 = (float)da[2];
     const int band = P.band_index[d];
@@ -159,58 +177,86 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
     const float pwv0 = (float)P.pwv0;
     int ip = 0, ie = 0;
     float* yrow = ymf + (lane >> 1) * 4 + (lane & 1);
-    for (int k = warp; k < Wn; k += F32_THREADS / 32) {
-      const Knot<float> kc = knots[k];
-      // direction of the detector minus direction of the boresight, horizon frame (coords/transforms.py:10-29)
-      const float dX = u * kc.ce - wm1 * kc.se;
-      const float dZ = u * kc.se + wm1 * kc.ce;
-      const float dNx = dX * kc.ca - Y * kc.sa;
-      const float dNy = dX * kc.sa + Y * kc.ca;
-      const float Nbx = -kc.se * kc.ca, Nby = -kc.se * kc.sa, Nbz = kc.ce;
-      const float Nz = Nbz + dZ;  // = sin(el) of the detector
-      const float inv = fast_rcp(Nbz * Nz);
-      const float dppx = (dNx * Nbz - Nbx * dZ) * inv;  // pp_d - pp_b (coordinates.py:333-349)
-      const float dppy = (dNy * Nbz - Nby * dZ) * inv;
-      float acc = 0.f;
-      bool bad = !(dppx == dppx) || !(dppy == dppy);
-      const LayerKnot<float>* lkk = lk + k;
-#pragma unroll 2
+    constexpr int NW = F32_THREADS / 32;
+    for (int kb = warp; kb < Wn; kb += NW * F32_G) {
+      float dppx[F32_G], dppy[F32_G], sinel[F32_G], acc[F32_G];
+      int kk[F32_G];
+      bool bad = false;
+#pragma unroll
+      for (int q = 0; q < F32_G; q++) {
+        kk[q] = min(kb + q * NW, Wn - 1);  // a short last group repeats the last knot (same value, same slot)
+        const Knot<float> kc = knots[kk[q]];
+        // direction of the detector minus direction of the boresight, horizon frame (coords/transforms.py:10-29)
+        const float dX = u * kc.ce - wm1 * kc.se;
+        const float dZ = u * kc.se + wm1 * kc.ce;
+        const float dNx = dX * kc.ca - Y * kc.sa;
+        const float dNy = dX * kc.sa + Y * kc.ca;
+        const float Nbx = -kc.se * kc.ca, Nby = -kc.se * kc.sa, Nbz = kc.ce;
+        const float Nz = Nbz + dZ;  // = sin(el) of the detector
+        const float inv = fast_rcp(Nbz * Nz);
+        dppx[q] = (dNx * Nbz - Nbx * dZ) * inv;  // pp_d - pp_b (coordinates.py:333-349)
+        dppy[q] = (dNy * Nbz - Nby * dZ) * inv;
+        sinel[q] = Nz;
+        acc[q] = 0.f;
+        bad = bad || !(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]);
+      }
+      unsigned badmask = 0;
       for (int l = 0; l < n_layers; l++) {
         const float4 Dm = *reinterpret_cast<const float4*>(&ls[l].D0);
         const int4 Ln = *reinterpret_cast<const int4*>(&ls[l].rms);
         const float* data = ls[l].data;
-        const LayerKnot<float> b = lkk[l * F32_W];
-        const float fx = fmaf(Dm.x, dppx, fmaf(Dm.y, dppy, b.fx));
-        const float fy = fmaf(Dm.z, dppx, fmaf(Dm.w, dppy, b.fy));
-        const float flx = floorf(fx), fly = floorf(fy);
-        int ix = b.ix + (int)flx, iy = b.iy + (int)fly;
-        float wx = fx - flx, wy = fy - fly;
-        if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
-          // rare: exactly on the last grid line is inside (RGI clips the index to n - 2); anything else is outside
-          if (ix == Ln.y && wx == 0.f) {
-            ix--;
-            wx = 1.f;
-          }
-          if (iy == Ln.z && wy == 0.f) {
-            iy--;
-            wy = 1.f;
-          }
+        float wx[F32_G], wy[F32_G];
+        const float* v[F32_G];
+#pragma unroll
+        for (int q = 0; q < F32_G; q++) {
+          const LayerKnot<float> b = lk[l * F32_W + kk[q]];
+          const float fx = fmaf(Dm.x, dppx[q], fmaf(Dm.y, dppy[q], b.fx));
+          const float fy = fmaf(Dm.z, dppx[q], fmaf(Dm.w, dppy[q], b.fy));
+          const float flx = floorf(fx), fly = floorf(fy);
+          int ix = b.ix + (int)flx, iy = b.iy + (int)fly;
+          wx[q] = fx - flx;
+          wy[q] = fy - fly;
           if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
-            record_out_of_grid(P.flags, l, d, wa + k);  // atmosphere.py:368-369
-            bad = true;
-            ix = iy = 0;
+            // rare: exactly on the last grid line is inside (RGI clips the index to n - 2); anything else is outside
+            if (ix == Ln.y && wx[q] == 0.f) {
+              ix--;
+              wx[q] = 1.f;
+            }
+            if (iy == Ln.z && wy[q] == 0.f) {
+              iy--;
+              wy[q] = 1.f;
+            }
+            if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
+              record_out_of_grid(P.flags, l, d, wa + kk[q]);  // atmosphere.py:368-369
+              badmask |= 1u << q;
+              ix = iy = 0;
+            }
           }
+          v[q] = data + (ix * Ln.w + iy);
         }
-        const float* v = data + (ix * Ln.w + iy);
-        const float v00 = __ldg(v), v01 = __ldg(v + 1), v10 = __ldg(v + Ln.w), v11 = __ldg(v + Ln.w + 1);
-        const float a = fmaf(wy, v01 - v00, v00), bb = fmaf(wy, v11 - v10, v10);
-        acc = fmaf(__int_as_float(Ln.x), fmaf(wx, bb - a, a), acc);
+        float v00[F32_G], v01[F32_G], v10[F32_G], v11[F32_G];
+#pragma unroll
+        for (int q = 0; q < F32_G; q++) {
+          v00[q] = __ldg(v[q]);
+          v01[q] = __ldg(v[q] + 1);
+          v10[q] = __ldg(v[q] + Ln.w);
+          v11[q] = __ldg(v[q] + Ln.w + 1);
+        }
+#pragma unroll
+        for (int q = 0; q < F32_G; q++) {
+          const float a = fmaf(wy[q], v01[q] - v00[q], v00[q]), bb = fmaf(wy[q], v11[q] - v10[q], v10[q]);
+          acc[q] = fmaf(__int_as_float(Ln.x), fmaf(wx[q], bb - a, a), acc[q]);
+        }
       }
-      if (bad) {
-        if (!(dppx == dppx) || !(dppy == dppy)) record_out_of_grid(P.flags, 0, d, wa + k);
-        acc = r_nan<float>();
+#pragma unroll
+      for (int q = 0; q < F32_G; q++) {
+        if (bad || ((badmask >> q) & 1)) {
+          if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, wa + kk[q]);
+          if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
+        }
+        const float y = loading_pW<float>(P, band, mu, pwv0 + acc[q], sinel[q], ip, ie);
+        if (kb + q * NW < Wn) yrow[kk[q] * (F32_NP * 4)] = y;
       }
-      yrow[k * (F32_NP * 4)] = loading_pW<float>(P, band, mu, pwv0 + acc, Nz, ip, ie);
     }
   }
   __syncthreads();
@@ -247,7 +293,6 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
   const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
   const double t_atm0 = P.t_atm0, inv_ts = 1.0 / P.timestep;
   const float inv_ts_f = (float)inv_ts;
-  const int n_t32 = (int)P.n_t;  // host guarantees 32 * n_t < 2^31
   const bool krj = units == MATM_UNITS_KRJ;
   const int npairs = nd >> 1;
   const float4* __restrict__ calq = P.calq;
@@ -269,9 +314,7 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
       SE = f2((float)bf.y, (float)bf.y);
     }
     const float4* yk = ym4 + li * F32_NP;
-    float* o0 = out + dbase * (int64_t)n_t32 + j;
-    float* o1 = o0 + n_t32;
-    const int64_t ostride = 2 * (int64_t)n_t32;
+    float* oj = out + j;
 #pragma unroll 4
     for (int p = 0; p < npairs; p++) {
       const float4 q0 = yk[p], q1 = yk[F32_NP + p];
@@ -308,10 +351,9 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
         }
         v = __fmul2_rn(v, f);
       }
-      *o0 = v.x;
-      *o1 = v.y;
-      o0 += ostride;
-      o1 += ostride;
+      const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
+      oj[ro.x] = v.x;
+      oj[ro.y] = v.y;
     }
     if (nd & 1) {  // odd tail detector of a partial tile
       const int p = npairs;
@@ -332,12 +374,12 @@ __global__ void __launch_bounds__(F32_THREADS, 3)
         }
         v *= f;
       }
-      *o0 = v;
+      oj[dc_row[2 * p]] = v;
     }
   }
 }
 
 static size_t synth_f32_smem(int n_layers) {
-  return (size_t)F32_W * F32_NP * sizeof(float4) + (5 * F32_W + 3) * sizeof(float) + F32_W * sizeof(Knot<float>) +
+  return (size_t)F32_W * F32_NP * sizeof(float4) + F32_SPLN * sizeof(float) + F32_W * sizeof(Knot<float>) +
          (size_t)n_layers * F32_W * sizeof(LayerKnot<float>);
 }
