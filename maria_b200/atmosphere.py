@@ -380,9 +380,17 @@ class Atmosphere:
     # ---------------------------------------------------------------------------------------------------------
     def generate(self):
         """Stage 1: run every AR process and beam-smooth every layer on the device (atmosphere.py:299-307,328-344)."""
+        self.generate_async()
+        self.finish_generate()
+
+    def generate_async(self):
+        """Start the AR recurrences of all processes on their own streams (one stream per process: the recurrences are
+        independent sequential chains of 1-3 CTAs each and run side by side).  Nothing the sampler reads is touched,
+        so a synthesis of the PREVIOUS realisation enqueued after this call overlaps with the chains: the next
+        realisation is generated while the current one is turned into TOD.  ``finish_generate`` completes the stage."""
         if not self._initialized:
             raise RuntimeError("Atmosphere must be initialized with a simulation.")
-        ctx, L = self.ctx, self.layers
+        ctx = self.ctx
         tc = ctx.torch
         cur = tc.cuda.current_stream(ctx.device)
         fork = cur.record_event()
@@ -390,7 +398,6 @@ class Atmosphere:
             self._streams = {k: tc.cuda.Stream(device=ctx.device) for k in self.processes}
         if not hasattr(self, "_layer_plan"):
             self._build_layer_plan()
-        # one stream per process: the 8 recurrences are independent sequential chains and run side by side
         for k, process in self.processes.items():
             stream = self._streams[k]
             stream.wait_event(fork)
@@ -399,6 +406,21 @@ class Atmosphere:
                     process.run(rng=self.rng)
                 else:
                     process.run(seed=self.seed, subsequence=k)
+        self._pending = True
+
+    def finish_generate(self):
+        """Beam-smooth the generated layers into the buffers the sampler reads (after everything enqueued so far on the
+        current stream, i.e. after any synthesis still reading the previous layers), and join the process streams."""
+        if not getattr(self, "_pending", False):
+            raise RuntimeError("finish_generate() without generate_async()")
+        ctx = self.ctx
+        tc = ctx.torch
+        cur = tc.cuda.current_stream(ctx.device)
+        readers_done = cur.record_event()
+        for k, process in self.processes.items():
+            stream = self._streams[k]
+            stream.wait_event(readers_done)
+            with tc.cuda.stream(stream):
                 st = ctx.stream_ptr()
                 for (li, col0, n_cols, sig_e, sig_x) in self._layer_plan[k]:
                     out, scratch = self._layer_dev[li]
@@ -408,6 +430,7 @@ class Atmosphere:
             cur.wait_stream(stream)
         if not getattr(self, "_layers_set", False):
             self.set_layers()
+        self._pending = False
         self._generated = True
 
     def _build_layer_plan(self):

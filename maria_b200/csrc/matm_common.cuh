@@ -13,7 +13,7 @@
 #include "../../include/maria_atm.h"
 
 #define MATM_ABI_VERSION 1
-#define MATM_CAL_SCALE 2048.0f  // bins per unit of t = sqrt(1 - sin el) in the fp32 calibration table
+#define MATM_CAL_SCALE 4096.0f  // bins per unit of t = sqrt(1 - sin el) in the fp32 calibration table
 
 // Device-side layer descriptor: everything the sampler needs per layer, in cell units.
 struct LayerDev {
@@ -59,10 +59,11 @@ struct SynthParams {
   const void* G2_R;        // (n_bands, npwv, nel)
   const void* Hc_R;        // (n_bands, nel-1): H(el) = Hc + Hs * el on el-interval i  (same line as the lerp of H1)
   const void* Hs_R;        // (n_bands, nel-1)
-  // fp32 fast path of a14: 1 / (factor k_B 1e12 H(el)) as piecewise quadratics in t = sqrt(1 - sin el) on uniform bins
-  // of width 1 / MATM_CAL_SCALE (see build_cal_table in matm_setup.cu)
-  const float4* calq;      // (n_bands, calq_n): {c0, c1, c2, w}; w = 0 plain bin, w > 0 index into calq_aux, w < 0 slow path
-  const float4* calq_aux;  // {c0, c1, c2, dt_kink}: the quadratic that applies for dt > dt_kink in a bin holding one kink
+  // fp32 fast path of a14: 1 / (factor k_B 1e12 H(el)) as one straight line per bin of t = sqrt(1 - sin el), bins of
+  // width 1 / MATM_CAL_SCALE (see build_cal_table in matm_setup.cu)
+  const float2* calq;      // (n_bands, calq_n): {c0, c1}, value = c0 + c1 dt, dt in [-1/2, 1/2]; c1 = NaN marks a special bin
+  const int* calq_kind;    // (n_bands, calq_n): 0 plain bin, k > 0 record k of calq_aux, < 0 generic slow path
+  const float4* calq_aux;  // 2 float4 per record: {c0, c1 for dt <= dt_k, c0, c1 for dt > dt_k}, {dt_k, 0, 0, 0}
   int calq_n;
   int table_ok;            // 0 if T0 / cal_T0 / cal_pwv left the table (results are NaN, as the reference)
   int* flags;              // [0] = status bits, [1] = layer, [2..3] = det (lo, hi), [4..5] = sample (lo, hi)
@@ -85,7 +86,9 @@ struct matm_handle {
   int32_t* band_index = nullptr;
   double *side_pwv = nullptr, *side_el = nullptr, *G2 = nullptr, *H1 = nullptr;
   void* tabR = nullptr;  // one allocation holding the R-typed tables
-  float4 *calq = nullptr, *calq_aux = nullptr;
+  float2* calq = nullptr;
+  int* calq_kind = nullptr;
+  float4* calq_aux = nullptr;
   // processing order of the detectors of a requested range (spatially coherent tiles; matm_detector_order)
   std::vector<float> det_xy_host;  // (n_det, 2) the atmosphere's offsets, kept for the ordering
   std::map<std::pair<int64_t, int64_t>, int32_t*> det_order;

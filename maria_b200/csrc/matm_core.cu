@@ -49,6 +49,7 @@ extern "C" int matm_destroy(matm_handle* h) {
   cudaFree(h->H1);
   cudaFree(h->tabR);
   cudaFree(h->calq);
+  cudaFree(h->calq_kind);
   for (auto& kv : h->det_order) cudaFree(kv.second);
   cudaFree(h->calq_aux);
   cudaFree(h->flags);

@@ -25,6 +25,9 @@
 #define F32_W (F32_KT + 1 + 2 * F32_HALO)
 #define F32_NP (F32_DT / 2)  // detector pairs per tile
 #define F32_SPLN ((5 * F32_W + 3) & ~3)  // floats reserved for the spline system (keeps what follows 16-byte aligned)
+#ifndef F32_S
+#define F32_S 4  // full-rate samples per thread and iteration in phase 3
+#endif
 #ifndef F32_G
 #define F32_G 4  // knots per thread and iteration in phase 1
 #endif
@@ -63,8 +66,15 @@ __device__ __forceinline__ float fast_asin(float x) {
   return copysignf(r, x);
 }
 
-// Exact (searching) evaluation of the calibration factor for the rare bins the table marks w < 0; raises the flag.
-__device__ __noinline__ float cal_factor_slow(const SynthParams& P, int band, float sin_el) {
+// The calibration factor in a special bin of the table (calq_kind != 0): a bin holding one grid point of the elevation
+// table has two lines, selected by the kink position; anything else goes through the exact searching code, which also
+// raises the flag when the elevation leaves the table.
+__device__ __noinline__ float cal_factor_special(const SynthParams& P, int idx, int band, float sin_el, float dt) {
+  const int kind = P.calq_kind[idx];
+  if (kind > 0) {
+    const float4 a = __ldg(P.calq_aux + 2 * kind), k = __ldg(P.calq_aux + 2 * kind + 1);
+    return dt > k.x ? fmaf(a.w, dt, a.z) : fmaf(a.y, dt, a.x);
+  }
   int ie = 0;
   const int ho = band * (P.nel - 1);
   const float den = cal_denominator<float>(P, reinterpret_cast<const float*>(P.sinel_R),
@@ -289,92 +299,99 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   }
   __syncthreads();
 
-  // ---- phase 3: evaluate at the full-rate samples of the tile; thread = sample, loop over detector pairs ----
+  // ---- phase 3: evaluate at the full-rate samples of the tile ----
+  // thread = F32_S samples (j, j + 256, ...), loop over detector PAIRS; the per-pair constants (offsets, table base,
+  // output rows) are fetched once per F32_S samples: the kernel is bound by L1 wavefronts, not by arithmetic.
   const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
   const double t_atm0 = P.t_atm0, inv_ts = 1.0 / P.timestep;
   const float inv_ts_f = (float)inv_ts;
   const bool krj = units == MATM_UNITS_KRJ;
   const int npairs = nd >> 1;
-  const float4* __restrict__ calq = P.calq;
+  const float2* __restrict__ calq = P.calq;
   const float2 scale2 = f2(MATM_CAL_SCALE, MATM_CAL_SCALE), magic2 = f2(12582912.f, 12582912.f);
-  for (int64_t j = j0 + tid; j < j1; j += F32_THREADS) {
-    const double tj = P.t_full[j];
-    int i = (int)floor((tj - t_atm0) * inv_ts);
-    i = min(max(i, k0), k1 - 1);
-    const int li = i - wa;
-    const float s = (float)(tj - P.t_atm[i]) * (spl[5 * li] * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
-    const float a0 = 1.f - s;
-    const float h26 = spl[5 * li + 1];
-    const float a2 = h26 * (a0 * a0 * a0 - a0), a3 = h26 * (s * s * s - s);
-    const float2 A0 = f2(a0, a0), A1 = f2(s, s), A2 = f2(a2, a2), A3 = f2(a3, a3);
-    float2 SE = f2(0.f, 0.f), CE = SE;
-    if (krj) {
-      const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
-      CE = f2((float)bf.x, (float)bf.x);
-      SE = f2((float)bf.y, (float)bf.y);
-    }
-    const float4* yk = ym4 + li * F32_NP;
-    float* oj = out + j;
-#pragma unroll 4
-    for (int p = 0; p < npairs; p++) {
-      const float4 q0 = yk[p], q1 = yk[F32_NP + p];
-      float2 v = __fmul2_rn(A0, f2(q0.x, q0.y));
-      v = __ffma2_rn(A1, f2(q1.x, q1.y), v);
-      v = __ffma2_rn(A2, f2(q0.z, q0.w), v);
-      v = __ffma2_rn(A3, f2(q1.z, q1.w), v);
+  for (int64_t jb = j0 + tid; jb < j1; jb += F32_THREADS * F32_S) {
+    float a0[F32_S], a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
+    const float4* yk[F32_S];
+    float* oj[F32_S];
+    bool ok[F32_S];
+#pragma unroll
+    for (int q = 0; q < F32_S; q++) {
+      const int64_t jq = jb + q * F32_THREADS;
+      ok[q] = jq < j1;
+      const int64_t j = ok[q] ? jq : j1 - 1;
+      const double tj = P.t_full[j];
+      int i = (int)floor((tj - t_atm0) * inv_ts);
+      i = min(max(i, k0), k1 - 1);
+      const int li = i - wa;
+      const float s = (float)(tj - P.t_atm[i]) * (spl[5 * li] * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
+      const float h26 = spl[5 * li + 1];
+      a0[q] = 1.f - s;
+      a1[q] = s;
+      a2[q] = h26 * (a0[q] * a0[q] * a0[q] - a0[q]);
+      a3[q] = h26 * (s * s * s - s);
+      se[q] = ce[q] = 0.f;
       if (krj) {
-        const float4 uw = dc_uw[p];
-        const int2 tb = dc_tab[p];
-        const float2 sn = __ffma2_rn(f2(uw.x, uw.y), SE, __fmul2_rn(f2(uw.z, uw.w), CE));  // sin(el), rolled offsets
-        const float2 t = f2(fast_sqrt(fmaxf(1.f - sn.x, 0.f)), fast_sqrt(fmaxf(1.f - sn.y, 0.f)));
-        const float2 x = __ffma2_rn(t, scale2, magic2);      // round(t * scale) in the low mantissa bits
-        const float2 r = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
-        const float2 dt = __ffma2_rn(t, scale2, f2(-r.x, -r.y));
-        const float4 c0 = __ldg(calq + (__float_as_int(x.x) + tb.x));
-        const float4 c1 = __ldg(calq + (__float_as_int(x.y) + tb.y));
-        float2 f;  // scalar on purpose: the operands sit in the registers of two different loads
-        f.x = fmaf(fmaf(c0.z, dt.x, c0.y), dt.x, c0.x);
-        f.y = fmaf(fmaf(c1.z, dt.y, c1.y), dt.y, c1.x);
-        if (c0.w != 0.f || c1.w != 0.f) {  // a bin with a grid point of the elevation table, or outside the table
-          if (c0.w > 0.f) {
-            const float4 a = __ldg(P.calq_aux + (int)c0.w);
-            if (dt.x > a.w) f.x = fmaf(fmaf(a.z, dt.x, a.y), dt.x, a.x);
-          } else if (c0.w < 0.f) {
-            f.x = cal_factor_slow(P, dc_band[2 * p], sn.x);
-          }
-          if (c1.w > 0.f) {
-            const float4 a = __ldg(P.calq_aux + (int)c1.w);
-            if (dt.y > a.w) f.y = fmaf(fmaf(a.z, dt.y, a.y), dt.y, a.x);
-          } else if (c1.w < 0.f) {
-            f.y = cal_factor_slow(P, dc_band[2 * p + 1], sn.y);
-          }
-        }
-        v = __fmul2_rn(v, f);
+        const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
+        ce[q] = (float)bf.x;
+        se[q] = (float)bf.y;
       }
-      const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
-      oj[ro.x] = v.x;
-      oj[ro.y] = v.y;
+      yk[q] = ym4 + li * F32_NP;
+      oj[q] = out + j;
     }
-    if (nd & 1) {  // odd tail detector of a partial tile
-      const int p = npairs;
-      const float4 q0 = yk[p], q1 = yk[F32_NP + p];
-      float v = fmaf(a3, q1.z, fmaf(a2, q0.z, fmaf(s, q1.x, a0 * q0.x)));
-      if (krj) {  // the same arithmetic as the paired path, so that any detector sharding gives identical bits
-        const float sn = fmaf(dc_uw[p].x, SE.x, dc_uw[p].z * CE.x);
-        const float t = fast_sqrt(fmaxf(1.f - sn, 0.f));
-        const float x = fmaf(t, MATM_CAL_SCALE, 12582912.f);
-        const float dt = fmaf(t, MATM_CAL_SCALE, -(x - 12582912.f));
-        const float4 c0 = __ldg(calq + (__float_as_int(x) + dc_tab[p].x));
-        float f = fmaf(fmaf(c0.z, dt, c0.y), dt, c0.x);
-        if (c0.w > 0.f) {
-          const float4 a = __ldg(P.calq_aux + (int)c0.w);
-          if (dt > a.w) f = fmaf(fmaf(a.z, dt, a.y), dt, a.x);
-        } else if (c0.w < 0.f) {
-          f = cal_factor_slow(P, dc_band[2 * p], sn);
+    for (int p = 0; p < npairs; p++) {
+      const float4 uw = dc_uw[p];
+      const int2 tb = dc_tab[p];
+      const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
+#pragma unroll
+      for (int q = 0; q < F32_S; q++) {
+        const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
+        float2 v = __fmul2_rn(f2(a0[q], a0[q]), f2(q0.x, q0.y));
+        v = __ffma2_rn(f2(a1[q], a1[q]), f2(q1.x, q1.y), v);
+        v = __ffma2_rn(f2(a2[q], a2[q]), f2(q0.z, q0.w), v);
+        v = __ffma2_rn(f2(a3[q], a3[q]), f2(q1.z, q1.w), v);
+        if (krj) {
+          const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
+          const float2 t = f2(fast_sqrt(fmaxf(1.f - sn.x, 0.f)), fast_sqrt(fmaxf(1.f - sn.y, 0.f)));
+          const float2 x = __ffma2_rn(t, scale2, magic2);  // round(t * scale) in the low mantissa bits
+          const float2 r = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
+          const float2 dt = __ffma2_rn(t, scale2, f2(-r.x, -r.y));
+          const int i0 = __float_as_int(x.x) + tb.x, i1 = __float_as_int(x.y) + tb.y;
+          const float2 c0 = __ldg(calq + i0), c1 = __ldg(calq + i1);
+          float2 f = f2(fmaf(c0.y, dt.x, c0.x), fmaf(c1.y, dt.y, c1.x));
+          if (!(f.x == f.x) || !(f.y == f.y)) {  // a bin with a grid point of the elevation table, or outside the table
+            if (!(f.x == f.x)) f.x = cal_factor_special(P, i0, dc_band[2 * p], sn.x, dt.x);
+            if (!(f.y == f.y)) f.y = cal_factor_special(P, i1, dc_band[2 * p + 1], sn.y, dt.y);
+          }
+          v = __fmul2_rn(v, f);
         }
-        v *= f;
+        if (ok[q]) {
+          oj[q][ro.x] = v.x;
+          oj[q][ro.y] = v.y;
+        }
       }
-      oj[dc_row[2 * p]] = v;
+    }
+    if (nd & 1) {  // odd tail detector of a partial tile; the same arithmetic as the paired path (bit-identical shards)
+      const int p = npairs;
+      const float uu = dc_uw[p].x, ww = dc_uw[p].z;
+      const int tbx = dc_tab[p].x;
+      const long long row = dc_row[2 * p];
+#pragma unroll
+      for (int q = 0; q < F32_S; q++) {
+        const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
+        float v = fmaf(a3[q], q1.z, fmaf(a2[q], q0.z, fmaf(a1[q], q1.x, a0[q] * q0.x)));
+        if (krj) {
+          const float sn = fmaf(uu, se[q], ww * ce[q]);
+          const float t = fast_sqrt(fmaxf(1.f - sn, 0.f));
+          const float x = fmaf(t, MATM_CAL_SCALE, 12582912.f);
+          const float dt = fmaf(t, MATM_CAL_SCALE, -(x - 12582912.f));
+          const int i0 = __float_as_int(x) + tbx;
+          const float2 c0 = __ldg(calq + i0);
+          float f = fmaf(c0.y, dt, c0.x);
+          if (!(f == f)) f = cal_factor_special(P, i0, dc_band[2 * p], sn, dt);
+          v *= f;
+        }
+        if (ok[q]) oj[q][row] = v;
+      }
     }
   }
 }
