@@ -395,7 +395,9 @@ class Atmosphere:
         cur = tc.cuda.current_stream(ctx.device)
         fork = cur.record_event()
         if not hasattr(self, "_streams"):
-            self._streams = {k: tc.cuda.Stream(device=ctx.device) for k in self.processes}
+            # high priority: a chain CTA needs a whole SM (512 threads x 128 registers), so when it runs underneath a
+            # synthesis kernel it must be first in line for the SMs that drain
+            self._streams = {k: tc.cuda.Stream(device=ctx.device, priority=-1) for k in self.processes}
         if not hasattr(self, "_layer_plan"):
             self._build_layer_plan()
         for k, process in self.processes.items():
@@ -432,6 +434,12 @@ class Atmosphere:
             self.set_layers()
         self._pending = False
         self._generated = True
+
+    def join_streams(self):
+        """Make the current stream wait for everything enqueued on the process streams."""
+        cur = self.ctx.torch.cuda.current_stream(self.ctx.device)
+        for stream in getattr(self, "_streams", {}).values():
+            cur.wait_stream(stream)
 
     def _build_layer_plan(self):
         """Per layer: its columns in the process, the beam-smoothing widths in cells (atmosphere.py:328-339) and the
@@ -506,7 +514,10 @@ class Atmosphere:
         """atmosphere.py:293-380.  Generates the layers; ``zenith_scaled_pwv`` is evaluated when read."""
         if not self._initialized:
             raise RuntimeError("Atmosphere must be initialized with a simulation.")
-        self.generate()
+        if getattr(self, "_pending", False):  # the chains were started ahead (Simulation.run pipelines observations)
+            self.finish_generate()
+        else:
+            self.generate()
         self.__dict__.pop("_zpwv_host", None)
 
     @property

@@ -8,6 +8,7 @@
 // in shared memory (staged once with the TMA bulk-copy engine) for all 2 n_ext steps, the gather vector is
 // rebuilt from the L2-resident BUFFER each step and the CTAs of the cluster meet at a hardware cluster barrier.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include "matm_common.cuh"
 
@@ -369,7 +370,17 @@ static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, cons
 static bool plan_v3(int n_cs, int n_sample, int* L, int* MP, int* cl) {
   static const int Ls[4] = {4, 8, 16, 32};
   static const int MPs[4] = {16, 24, 32, 40};
+  static int min_l = -1;  // MATM_AR_MINL: lower bound on the lanes per row (tuning knob; more lanes = shorter per-thread chain)
+  if (min_l < 0) {
+    const char* e = getenv("MATM_AR_MINL");
+    min_l = e ? atoi(e) : 0;
+  }
   for (int li = 0; li < 4; li++) {
+    if (Ls[li] < min_l && li < 3) {
+      // only skip when a larger L still fits the cluster limit
+      const int rows_next = (AR_THREADS / 32) * (32 / Ls[li + 1]);
+      if ((n_cs + rows_next - 1) / rows_next <= 8 && n_sample <= Ls[li + 1] * 40) continue;
+    }
     if (n_sample > Ls[li] * 40) continue;
     int mp = 0;
     for (int mi = 0; mi < 4; mi++)

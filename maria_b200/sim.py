@@ -108,15 +108,23 @@ class Simulation(AtmosphereMixin):
 
     def run(self, units="K_RJ"):
         """:201-211 -- one TOD per plan, in ``units``."""
-        return [self.run_obs(obs, units=units) for obs in self.obs_list]
+        tods = []
+        for k, obs in enumerate(self.obs_list):
+            nxt = self.obs_list[k + 1].atmosphere if k + 1 < len(self.obs_list) else None
+            tods.append(self.run_obs(obs, units=units, prefetch=nxt))
+        return tods
 
-    def run_obs(self, obs, units="pW"):
+    def run_obs(self, obs, units="pW", prefetch=None):
         """:213-272, atmosphere branch; the reference builds the pW TOD and converts, here both happen in the kernel."""
         atm = obs.atmosphere
         if atm is None:
             raise RuntimeError("this build synthesises the atmosphere field only: pass atmosphere='2d'")
         dets = obs.instrument.dets
         self._simulate_atmosphere(obs)  # :216-221 (generates the layers)
+        if prefetch is not None and prefetch.noise == "philox" and prefetch is not atm:
+            # device noise has no host draw order to respect: start the next observation's AR chains now, so that they
+            # run (on a handful of SMs) underneath this observation's synthesis kernel
+            prefetch.generate_async()
         gain_error = np.exp(dets.gain_error * atm.rng.standard_normal(size=dets.n))  # :239-241
         atm.set_gain(gain_error)
         det0, n_det = self.det_range if self.det_range is not None else (0, dets.n)
