@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--depth", type=int, default=2, help="realisations whose AR chains are in flight underneath the synthesis")
     ap.add_argument("--no-overlap", action="store_true",
                     help="generate and synthesise strictly one after the other (default: the AR chains of realisation i+1 run "
                          "underneath the synthesis kernel of realisation i)")
@@ -215,7 +216,7 @@ def run_b200(args):
     sim = M.Simulation(cfg["instrument"], cfg["plan"], cfg["site"], atmosphere="2d", dtype=np.float32,
                        det_range=(rank * args.n_det, args.n_det),
                        atmosphere_kwargs=dict(weather=cfg["weather"], spectrum=cfg["spectrum"], noise="philox", seed=1234,
-                                              device=local))
+                                              device=local, pipeline_depth=1 if args.no_overlap else max(1, args.depth)))
     setup_s = time.perf_counter() - t0
     obs = sim.obs_list[0]
     atm = obs.atmosphere
@@ -235,9 +236,9 @@ def run_b200(args):
         realisation's synthesis kernel and run underneath it (they occupy ~11 SMs); every step still contains exactly one
         chain set, one smoothing pass and one synthesis."""
         if overlap:
-            atm.finish_generate()        # beam-smooth realisation i (its chains were started during step i - 1)
-            atm.seed = 1235 + i
-            atm.generate_async()         # chains of realisation i + 1
+            atm.finish_generate()        # beam-smooth realisation i (its chains were started `depth` steps ago)
+            atm.seed = 1234 + depth + i
+            atm.generate_async()         # chains of realisation i + depth
         else:
             atm.seed = 1234 + i          # a fresh realisation every step: nothing can be cached
             atm.generate()
@@ -253,9 +254,11 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     n_warm = max(args.warmup, 3)
+    depth = atm.pipeline_depth
     if overlap:
-        atm.seed = 1234
-        atm.generate_async()  # pipeline prologue: realisation 0
+        for r in range(depth):  # pipeline prologue: realisations 0 .. depth - 1
+            atm.seed = 1234 + r
+            atm.generate_async()
     for i in range(n_warm):
         step(i)
     barrier()  # drains the chains of the first timed realisation too: the timed region holds exactly K of everything
@@ -317,8 +320,9 @@ def run_b200(args):
                        "layers": [[p.n_extrusion, p.n_cross_section] for p in atm.processes.values()],
                        "l2": "output (n_det*n_t*4 B per step) is far larger than L2; layers are regenerated every step",
                        "rng": "philox (device)", "setup_s": setup_s, "status": status,
-                       "pipeline": ("AR chains of realisation i+1 overlap the synthesis of realisation i; the timed region holds "
-                                    "exactly K chain sets, K smoothing passes and K syntheses") if overlap else "sequential"},
+                       "pipeline": (f"AR chains of realisations i+1..i+{depth} run underneath the synthesis of realisation i; the "
+                                    "timed region holds exactly K chain sets, K smoothing passes and K syntheses") if overlap
+                       else "sequential", "pipeline_depth": depth if overlap else 0},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
@@ -352,6 +356,7 @@ def run_e2e(args, torch, dist, world, local, sim, cfg, gain, out_dev, barrier):
         atm.generate()
         atm.synthesize_host(host_out, det0, n_det, units="K_RJ", apply_gain=True)
 
+    atm.drain()
     step(0)
     barrier()
     t0 = time.perf_counter()

@@ -127,19 +127,21 @@ class AutoregressiveProcess:
                      f"{ttime.monotonic() - t0:.3f} s")
 
     # ---- device side ----
-    def bind(self, ctx):
-        """Upload A, B and the stencil; allocate BUFFER (3 n_ext, n_cs) and Z (2 n_ext, n_cs) on the device."""
+    def bind(self, ctx, n_slots=1):
+        """Upload A, B and the stencil; allocate BUFFER (3 n_ext, n_cs) and Z (2 n_ext, n_cs) on the device, once per
+        pipeline slot (``n_slots`` realisations can be in flight at the same time)."""
         tc = ctx.torch
         self._ctx = ctx
+        self._slot = 0
         self._dev = dict(
             A=ctx.to_device(self.A, tc.float64), B=ctx.to_device(self.B, tc.float64),
             esi=ctx.to_device(self.extrusion_sample_index.astype(np.int32), tc.int32),
             csi=ctx.to_device(self.cross_section_sample_index.astype(np.int32), tc.int32),
-            buffer=ctx.empty((3 * self.n_extrusion, self.n_cross_section), tc.float64),
-            z=ctx.empty((2 * self.n_extrusion, self.n_cross_section), tc.float64),
+            buffer=[ctx.empty((3 * self.n_extrusion, self.n_cross_section), tc.float64) for _ in range(n_slots)],
+            z=[ctx.empty((2 * self.n_extrusion, self.n_cross_section), tc.float64) for _ in range(n_slots)],
         )
 
-    def run(self, rng=None, seed=None, subsequence=0):
+    def run(self, rng=None, seed=None, subsequence=0, slot=0):
         """process.py:191-209.  ``rng`` (host, e.g. ``np.random``): validation mode, the noise is drawn on the host in
         the reference's order and uploaded.  ``seed``: production mode, Philox noise on the device."""
         if self._dev is None:
@@ -147,27 +149,27 @@ class AutoregressiveProcess:
         ctx, dv = self._ctx, self._dev
         n_ext, n_cs = self.n_extrusion, self.n_cross_section
         st = ctx.stream_ptr()
-        tail = dv["buffer"][2 * n_ext:]
+        buf, zz = dv["buffer"][slot], dv["z"][slot]
+        tail = buf[2 * n_ext:]
         if rng is not None:
             buffer0 = rng.standard_normal((3 * n_ext, n_cs))  # process.py:196-198 (only the last n_ext rows are read)
             z = rng.standard_normal((2 * n_ext, n_cs))        # process.py:206, one row per executed step
             tail.copy_(ctx.torch.from_numpy(buffer0[2 * n_ext:]))
-            dv["z"].copy_(ctx.torch.from_numpy(z))
+            zz.copy_(ctx.torch.from_numpy(z))
         else:
             if seed is None:
                 raise ValueError("either a host rng or a Philox seed is required")
             ctx.check(ctx.lib.matm_fill_normal(ctx.h, tail.data_ptr(), tail.numel(), seed, 2 * subsequence, st))
-            ctx.check(ctx.lib.matm_fill_normal(ctx.h, dv["z"].data_ptr(), dv["z"].numel(), seed, 2 * subsequence + 1, st))
+            ctx.check(ctx.lib.matm_fill_normal(ctx.h, zz.data_ptr(), zz.numel(), seed, 2 * subsequence + 1, st))
         ctx.check(ctx.lib.matm_ar_generate(ctx.h, n_ext, n_cs, self.n_sample, self.n_near, dv["A"].data_ptr(), dv["B"].data_ptr(),
-                                           dv["esi"].data_ptr(), dv["csi"].data_ptr(), dv["buffer"].data_ptr(),
-                                           dv["z"].data_ptr(), st))
+                                           dv["esi"].data_ptr(), dv["csi"].data_ptr(), buf.data_ptr(), zz.data_ptr(), st))
         self._values_host = None
-        return self.values_device
+        return buf[:n_ext]
 
     @property
     def values_device(self):
         """(n_ext, n_cs) float64 view of the generated field on the device."""
-        return self._dev["buffer"][: self.n_extrusion]
+        return self._dev["buffer"][self._slot][: self.n_extrusion]
 
     @property
     def values(self):
@@ -227,7 +229,8 @@ class Atmosphere:
     def __init__(self, model="2d", timestamp=None, region="princeton", altitude=None, weather=None,
                  weather_quantiles=None, weather_source="era5", spectrum_source="am", pwv_rms_frac=0.03,
                  max_height=5e3, timestep=None, interpolation_method="linear", disable_progress_bars=False, *,
-                 spectrum=None, device=0, precision="fp32", noise="host", seed=1234, rng=None, geometry="auto"):
+                 spectrum=None, device=0, precision="fp32", noise="host", seed=1234, rng=None, geometry="auto",
+                 pipeline_depth=1):
         if model not in SUPPORTED_MODELS_LIST:
             raise ValueError(f"Invalid model '{model}'. Supported models are {SUPPORTED_MODELS_LIST}.")
         if noise not in ("host", "philox"):
@@ -250,6 +253,7 @@ class Atmosphere:
         self.device, self.precision, self.noise, self.seed = device, precision, noise, seed
         self.rng = rng if rng is not None else np.random
         self.geometry = geometry
+        self.pipeline_depth = max(1, int(pipeline_depth))  # realisations whose AR chains may be in flight at once
         self._initialized = False
         self._generated = False
 
@@ -333,7 +337,8 @@ class Atmosphere:
         self._bind_scan_and_detectors(obs, None)
         self.set_bands(obs.instrument.dets)
         for p in self.processes.values():
-            p.bind(self.ctx)
+            p.bind(self.ctx, self.pipeline_depth)
+        self._pending_slots, self._issued = [], 0
         self._layer_dev = {}
 
     def _bind_scan_and_detectors(self, obs, gain):
@@ -384,12 +389,15 @@ class Atmosphere:
         self.finish_generate()
 
     def generate_async(self):
-        """Start the AR recurrences of all processes on their own streams (one stream per process: the recurrences are
-        independent sequential chains of 1-3 CTAs each and run side by side).  Nothing the sampler reads is touched,
-        so a synthesis of the PREVIOUS realisation enqueued after this call overlaps with the chains: the next
-        realisation is generated while the current one is turned into TOD.  ``finish_generate`` completes the stage."""
+        """Start the AR recurrences of all processes for one more realisation, on their own high-priority streams (one
+        stream per process and pipeline slot: the recurrences are independent sequential chains of 1-3 CTAs each and
+        run side by side).  Nothing the sampler reads is touched, so a synthesis of an EARLIER realisation enqueued after
+        this call overlaps with the chains: up to ``pipeline_depth`` realisations are generated underneath the synthesis
+        kernels.  ``finish_generate`` completes the oldest one."""
         if not self._initialized:
             raise RuntimeError("Atmosphere must be initialized with a simulation.")
+        if len(self._pending_slots) >= self.pipeline_depth:
+            raise RuntimeError(f"{len(self._pending_slots)} realisations are already in flight (pipeline_depth={self.pipeline_depth})")
         ctx = self.ctx
         tc = ctx.torch
         cur = tc.cuda.current_stream(ctx.device)
@@ -397,31 +405,41 @@ class Atmosphere:
         if not hasattr(self, "_streams"):
             # high priority: a chain CTA needs a whole SM (512 threads x 128 registers), so when it runs underneath a
             # synthesis kernel it must be first in line for the SMs that drain
-            self._streams = {k: tc.cuda.Stream(device=ctx.device, priority=-1) for k in self.processes}
+            self._streams = {(s, k): tc.cuda.Stream(device=ctx.device, priority=-1)
+                             for s in range(self.pipeline_depth) for k in self.processes}
         if not hasattr(self, "_layer_plan"):
             self._build_layer_plan()
+        slot = self._issued % self.pipeline_depth
+        self._issued += 1
         for k, process in self.processes.items():
-            stream = self._streams[k]
+            stream = self._streams[(slot, k)]
             stream.wait_event(fork)
             with tc.cuda.stream(stream):
                 if self.noise == "host":
-                    process.run(rng=self.rng)
+                    process.run(rng=self.rng, slot=slot)
                 else:
-                    process.run(seed=self.seed, subsequence=k)
-        self._pending = True
+                    process.run(seed=self.seed, subsequence=k, slot=slot)
+        self._pending_slots.append(slot)
+
+    @property
+    def _pending(self):
+        return len(self._pending_slots) > 0
 
     def finish_generate(self):
-        """Beam-smooth the generated layers into the buffers the sampler reads (after everything enqueued so far on the
-        current stream, i.e. after any synthesis still reading the previous layers), and join the process streams."""
-        if not getattr(self, "_pending", False):
+        """Beam-smooth the oldest realisation in flight into the buffers the sampler reads (after everything enqueued so
+        far on the current stream, i.e. after any synthesis still reading the previous layers), and join its streams."""
+        if not self._pending_slots:
             raise RuntimeError("finish_generate() without generate_async()")
         ctx = self.ctx
         tc = ctx.torch
         cur = tc.cuda.current_stream(ctx.device)
         readers_done = cur.record_event()
+        slot = self._pending_slots.pop(0)
         for k, process in self.processes.items():
-            stream = self._streams[k]
+            stream = self._streams[(slot, k)]
             stream.wait_event(readers_done)
+            process._slot = slot
+            process._values_host = None
             with tc.cuda.stream(stream):
                 st = ctx.stream_ptr()
                 for (li, col0, n_cols, sig_e, sig_x) in self._layer_plan[k]:
@@ -432,8 +450,12 @@ class Atmosphere:
             cur.wait_stream(stream)
         if not getattr(self, "_layers_set", False):
             self.set_layers()
-        self._pending = False
         self._generated = True
+
+    def drain(self):
+        """Complete every realisation still in flight (the last one stays in the sampler's buffers)."""
+        while self._pending_slots:
+            self.finish_generate()
 
     def join_streams(self):
         """Make the current stream wait for everything enqueued on the process streams."""
@@ -514,7 +536,7 @@ class Atmosphere:
         """atmosphere.py:293-380.  Generates the layers; ``zenith_scaled_pwv`` is evaluated when read."""
         if not self._initialized:
             raise RuntimeError("Atmosphere must be initialized with a simulation.")
-        if getattr(self, "_pending", False):  # the chains were started ahead (Simulation.run pipelines observations)
+        if self._pending:  # the chains were started ahead (Simulation.run pipelines observations)
             self.finish_generate()
         else:
             self.generate()

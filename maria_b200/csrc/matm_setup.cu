@@ -1,6 +1,7 @@
 // Set-up entry points: scan, layers, detectors, band tables.  Small host arrays are uploaded and the derived
 // per-time / per-detector / per-band constants are evaluated on the device in float64.
 #include <algorithm>
+#include <math.h>
 
 #include "matm_common.cuh"
 
@@ -100,6 +101,11 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_ho
   if (!t_atm_host || !az_atm_host || !el_atm_host || !t_host || !el_host) MATM_FAIL_ARG(h, "matm_set_scan: null pointer");
   for (int k = 1; k < n_t_atm; k++)
     if (!(t_atm_host[k] > t_atm_host[k - 1])) MATM_FAIL_ARG(h, "matm_set_scan: knot times must increase");
+  for (int k = 0; k < n_t_atm; k++)
+    if (!isfinite(az_atm_host[k]) || !isfinite(el_atm_host[k])) MATM_FAIL_ARG(h, "matm_set_scan: boresight az / el must be finite");
+  for (int64_t j = 0; j < n_t; j++)
+    if (!isfinite(el_host[j]) || !isfinite(t_host[j])) MATM_FAIL_ARG(h, "matm_set_scan: full-rate time / elevation must be finite");
+  if (n_t > (int64_t)INT32_MAX) MATM_FAIL_ARG(h, "matm_set_scan: more than 2^31 - 1 samples per detector; split the scan in time");
   (void)az_host;  // the full-rate azimuth does not enter the path (only the elevation does, tod.py:126-133)
   const double t_atm0 = t_atm_host[0];
   double *az_d = nullptr, *el_d = nullptr, *elf_d = nullptr;
@@ -244,6 +250,8 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   if (matm_set_device(h)) return MATM_ERR_CUDA;
   if (n_det < 1 || !offsets_atm_host || !offsets_full_host || !band_index_host || !mueller00_host)
     MATM_FAIL_ARG(h, "matm_set_detectors: bad arguments");
+  for (int64_t i = 0; i < 2 * n_det; i++)
+    if (!isfinite(offsets_atm_host[i]) || !isfinite(offsets_full_host[i])) MATM_FAIL_ARG(h, "matm_set_detectors: offsets must be finite");
   double *oa = nullptr, *of = nullptr;
   int rc;
   if ((rc = matm_upload(h, &oa, offsets_atm_host, (size_t)n_det * 2))) return rc;

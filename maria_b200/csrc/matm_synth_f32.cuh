@@ -26,7 +26,7 @@
 #define F32_NP (F32_DT / 2)  // detector pairs per tile
 #define F32_SPLN ((5 * F32_W + 3) & ~3)  // floats reserved for the spline system (keeps what follows 16-byte aligned)
 #ifndef F32_S
-#define F32_S 4  // full-rate samples per thread and iteration in phase 3
+#define F32_S 3  // full-rate samples per thread and iteration in phase 3 (4 spills at 80 registers)
 #endif
 #ifndef F32_G
 #define F32_G 4  // knots per thread and iteration in phase 1
@@ -50,6 +50,12 @@ __device__ __forceinline__ float fast_rcp(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
+}
+// row[j] = v with the address formed by one mad.wide (the compiler otherwise re-associates it into six instructions)
+__device__ __forceinline__ void st_row(float* row, int j, float v) {
+  float* a;
+  asm("mad.wide.s32 %0, %1, 4, %2;" : "=l"(a) : "r"(j), "l"(row));
+  asm volatile("st.global.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
 }
 // asin on [-1, 1]: pi/2 - sqrt(1 - |x|) P7(|x|)  (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 rad)
 __device__ __forceinline__ float fast_asin(float x) {
@@ -310,24 +316,22 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   const float2* __restrict__ calq = P.calq;
   const float2 scale2 = f2(MATM_CAL_SCALE, MATM_CAL_SCALE), magic2 = f2(12582912.f, 12582912.f);
   for (int64_t jb = j0 + tid; jb < j1; jb += F32_THREADS * F32_S) {
-    float a0[F32_S], a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
+    float a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
     const float4* yk[F32_S];
-    float* oj[F32_S];
-    bool ok[F32_S];
+    int jq[F32_S];
 #pragma unroll
     for (int q = 0; q < F32_S; q++) {
-      const int64_t jq = jb + q * F32_THREADS;
-      ok[q] = jq < j1;
-      const int64_t j = ok[q] ? jq : j1 - 1;
+      // a sample index past the tile repeats the tile's last sample: the same value is stored to the same address by
+      // the thread that owns it, which is harmless and keeps the inner loop free of predicates
+      const int64_t j = min(jb + q * F32_THREADS, j1 - 1);
       const double tj = P.t_full[j];
       int i = (int)floor((tj - t_atm0) * inv_ts);
       i = min(max(i, k0), k1 - 1);
       const int li = i - wa;
       const float s = (float)(tj - P.t_atm[i]) * (spl[5 * li] * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
-      const float h26 = spl[5 * li + 1];
-      a0[q] = 1.f - s;
+      const float h26 = spl[5 * li + 1], c = 1.f - s;
       a1[q] = s;
-      a2[q] = h26 * (a0[q] * a0[q] * a0[q] - a0[q]);
+      a2[q] = h26 * (c * c * c - c);
       a3[q] = h26 * (s * s * s - s);
       se[q] = ce[q] = 0.f;
       if (krj) {
@@ -336,52 +340,56 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
         se[q] = (float)bf.y;
       }
       yk[q] = ym4 + li * F32_NP;
-      oj[q] = out + j;
+      jq[q] = (int)j;
     }
+#pragma unroll 2
     for (int p = 0; p < npairs; p++) {
       const float4 uw = dc_uw[p];
       const int2 tb = dc_tab[p];
       const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
+      float* r0 = out + ro.x;
+      float* r1 = out + ro.y;
+      asm("" : "+l"(r0), "+l"(r1));  // keep the row pointers as they are: each store is then one mad.wide + one st
 #pragma unroll
       for (int q = 0; q < F32_S; q++) {
         const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
-        float2 v = __fmul2_rn(f2(a0[q], a0[q]), f2(q0.x, q0.y));
+        const float a0 = 1.f - a1[q];
+        float2 v = __fmul2_rn(f2(a0, a0), f2(q0.x, q0.y));
         v = __ffma2_rn(f2(a1[q], a1[q]), f2(q1.x, q1.y), v);
         v = __ffma2_rn(f2(a2[q], a2[q]), f2(q0.z, q0.w), v);
         v = __ffma2_rn(f2(a3[q], a3[q]), f2(q1.z, q1.w), v);
         if (krj) {
           const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
-          const float2 t = f2(fast_sqrt(fmaxf(1.f - sn.x, 0.f)), fast_sqrt(fmaxf(1.f - sn.y, 0.f)));
+          // |1 - sin el|: sin el can exceed 1 by an ulp; inputs are finite (checked by matm_set_scan / matm_set_detectors)
+          const float2 t = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));
           const float2 x = __ffma2_rn(t, scale2, magic2);  // round(t * scale) in the low mantissa bits
           const float2 r = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
           const float2 dt = __ffma2_rn(t, scale2, f2(-r.x, -r.y));
           const int i0 = __float_as_int(x.x) + tb.x, i1 = __float_as_int(x.y) + tb.y;
           const float2 c0 = __ldg(calq + i0), c1 = __ldg(calq + i1);
           float2 f = f2(fmaf(c0.y, dt.x, c0.x), fmaf(c1.y, dt.y, c1.x));
-          if (!(f.x == f.x) || !(f.y == f.y)) {  // a bin with a grid point of the elevation table, or outside the table
+          if (!(f.x * f.y == f.x * f.y)) {  // a bin with a grid point of the elevation table, or outside the table
             if (!(f.x == f.x)) f.x = cal_factor_special(P, i0, dc_band[2 * p], sn.x, dt.x);
             if (!(f.y == f.y)) f.y = cal_factor_special(P, i1, dc_band[2 * p + 1], sn.y, dt.y);
           }
           v = __fmul2_rn(v, f);
         }
-        if (ok[q]) {
-          oj[q][ro.x] = v.x;
-          oj[q][ro.y] = v.y;
-        }
+        st_row(r0, jq[q], v.x);
+        st_row(r1, jq[q], v.y);
       }
     }
     if (nd & 1) {  // odd tail detector of a partial tile; the same arithmetic as the paired path (bit-identical shards)
       const int p = npairs;
       const float uu = dc_uw[p].x, ww = dc_uw[p].z;
       const int tbx = dc_tab[p].x;
-      const long long row = dc_row[2 * p];
+      float* __restrict__ r0 = out + dc_row[2 * p];
 #pragma unroll
       for (int q = 0; q < F32_S; q++) {
         const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
-        float v = fmaf(a3[q], q1.z, fmaf(a2[q], q0.z, fmaf(a1[q], q1.x, a0[q] * q0.x)));
+        float v = fmaf(a3[q], q1.z, fmaf(a2[q], q0.z, fmaf(a1[q], q1.x, (1.f - a1[q]) * q0.x)));
         if (krj) {
           const float sn = fmaf(uu, se[q], ww * ce[q]);
-          const float t = fast_sqrt(fmaxf(1.f - sn, 0.f));
+          const float t = fast_sqrt(fabsf(1.f - sn));
           const float x = fmaf(t, MATM_CAL_SCALE, 12582912.f);
           const float dt = fmaf(t, MATM_CAL_SCALE, -(x - 12582912.f));
           const int i0 = __float_as_int(x) + tbx;
@@ -390,7 +398,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
           if (!(f == f)) f = cal_factor_special(P, i0, dc_band[2 * p], sn, dt);
           v *= f;
         }
-        if (ok[q]) oj[q][row] = v;
+        st_row(r0, jq[q], v);
       }
     }
   }
