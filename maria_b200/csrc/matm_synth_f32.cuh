@@ -17,7 +17,7 @@
 #define F32_KT 128   // spline intervals per tile
 #endif
 #ifndef F32_HALO
-#define F32_HALO 12  // extra knots each side; the error of the artificial boundary decays as (2 - sqrt 3)^HALO
+#define F32_HALO 10  // extra knots each side; the error of the artificial boundary decays as (2 - sqrt 3)^HALO
 #endif
 #ifndef F32_MINB
 #define F32_MINB 3   // CTAs per SM the register allocation is held to
@@ -95,8 +95,9 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   extern __shared__ __align__(16) unsigned char dyn[];
   float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_d0, y_d1, m_d0, m_d1}
   float* ymf = reinterpret_cast<float*>(dyn);
-  float* spl = reinterpret_cast<float*>(ym4 + F32_W * F32_NP);       // [W][5]
-  Knot<float>* knots = reinterpret_cast<Knot<float>*>(spl + F32_SPLN);
+  float4* splq = ym4 + F32_W * F32_NP;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
+  float* h26 = reinterpret_cast<float*>(splq + F32_W);               // [W] h_k^2 / 6
+  Knot<float>* knots = reinterpret_cast<Knot<float>*>(reinterpret_cast<float*>(splq) + F32_SPLN);
   LayerKnot<float>* lk = reinterpret_cast<LayerKnot<float>*>(knots + F32_W);  // [n_layers][W]
   __shared__ __align__(16) LayerF ls[MATM_MAX_LAYERS];
   __shared__ float4 dc_uw[F32_NP];  // {u_d0, u_d1, w_d0, w_d1} of the rolled offsets
@@ -177,7 +178,11 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     uw[(dd >> 1) * 4 + 2 + (dd & 1)] = w;
     reinterpret_cast<int*>(dc_tab)[dd] = band * P.calq_n - MAGIC_BITS;
   }
-  for (int e = tid; e < 5 * Wn; e += F32_THREADS) spl[e] = (float)P.spl[5 * (size_t)wa + e];
+  for (int k = tid; k < Wn; k += F32_THREADS) {
+    const double* sp = P.spl + 5 * (size_t)(wa + k);
+    splq[k] = make_float4((float)sp[0], (float)sp[2], (float)sp[3], (float)sp[4]);
+    h26[k] = (float)sp[1];
+  }
   __syncthreads();
 
   // ---- phase 1: loading [pW] at the window's knots ----
@@ -191,6 +196,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     const int band = P.band_index[d];
     const float mu = (float)P.mueller00[d];
     const float pwv0 = (float)P.pwv0;
+    const float gain_d = dc_gain[lane];
     int ip = 0, ie = 0;
     float* yrow = ymf + (lane >> 1) * 4 + (lane & 1);
     constexpr int NW = F32_THREADS / 32;
@@ -271,37 +277,50 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
           if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
         }
         const float y = loading_pW<float>(P, band, mu, pwv0 + acc[q], sinel[q], ip, ie);
-        if (kb + q * NW < Wn) yrow[kk[q] * (F32_NP * 4)] = y;
+        if (kb + q * NW < Wn) yrow[kk[q] * (F32_NP * 4)] = y * gain_d;  // the spline is linear in the data: gain goes in here
       }
     }
   }
   __syncthreads();
 
-  // ---- phase 2: spline second derivatives (see the generic kernel for the derivation); warp 0, lane = detector ----
+  // ---- phase 2: second derivatives M_k of the not-a-knot cubic spline through the window's knots; warp 0, lane = detector.
+  // Rows of the global tridiagonal system, swept with the global elimination factors.  At a true end of the series the
+  // sweep starts / ends exactly; at an artificial end it starts from the locally-constant guess M = d / (a + b + c),
+  // whose error decays by (2 - sqrt 3) per knot across the halo.
   if (warp == 0) {
     float* row = ymf + (lane >> 1) * 4 + (lane & 1);
     constexpr int RS = F32_NP * 4;  // stride between knots, in floats
-    auto yv = [&](int k) { return row[k * RS]; };
-    auto mref = [&](int k) -> float& { return row[k * RS + 2]; };
-    auto invh = [&](int k) { return spl[5 * k + 0]; };
-    auto rhs = [&](int k) { return 6.f * ((yv(k + 1) - yv(k)) * invh(k) - (yv(k) - yv(k - 1)) * invh(k - 1)); };
-    auto guess = [&](int k) { return rhs(k) / (3.f * (1.f / invh(k - 1) + 1.f / invh(k))); };
     const int lo = 1, hi = Wn - 2;
-    float dp = (wa == 0) ? rhs(lo) * spl[5 * lo + 2] : guess(lo) * (1.f + spl[5 * lo + 4]);
-    mref(lo) = dp;
+    float y0 = row[0], y1 = row[RS], y2 = row[2 * RS];
+    float4 sp0 = splq[0], sp1 = splq[1];
+    auto rhs3 = [](float ya, float yb, float yc, float iha, float ihb) { return 6.f * ((yc - yb) * ihb - (yb - ya) * iha); };
+    const float r_lo = rhs3(y0, y1, y2, sp0.x, sp1.x);
+    float dp = (wa == 0) ? r_lo * sp1.y : r_lo / (3.f * (1.f / sp0.x + 1.f / sp1.x)) * (1.f + sp1.w);
+    row[lo * RS + 2] = dp;
+    float r_k = r_lo;
     for (int k = lo + 1; k <= hi; k++) {
-      dp = rhs(k) * spl[5 * k + 2] - spl[5 * k + 3] * dp;
-      mref(k) = dp;
+      y0 = y1;
+      y1 = y2;
+      y2 = row[(k + 1) * RS];
+      sp0 = sp1;
+      sp1 = splq[k];
+      r_k = rhs3(y0, y1, y2, sp0.x, sp1.x);
+      dp = fmaf(r_k, sp1.y, -sp1.z * dp);
+      row[k * RS + 2] = dp;
     }
-    if (wb != n - 1) mref(hi) -= spl[5 * hi + 4] * guess(hi);
-    for (int k = hi - 1; k >= lo; k--) mref(k) -= spl[5 * k + 4] * mref(k + 1);
-    mref(0) = (wa == 0) ? mref(1) - (invh(1) / invh(0)) * (mref(2) - mref(1)) : mref(1);
-    mref(Wn - 1) = (wb == n - 1) ? mref(Wn - 2) + (invh(Wn - 3) / invh(Wn - 2)) * (mref(Wn - 2) - mref(Wn - 3)) : mref(Wn - 2);
-    const float g = dc_gain[lane];  // the spline is linear in the data: fold the detector gain in here
-    for (int k = 0; k < Wn; k++) {
-      row[k * RS] *= g;
-      row[k * RS + 2] *= g;
+    float mk = dp;  // M at hi
+    if (wb != n - 1) {
+      mk -= sp1.w * (r_k / (3.f * (1.f / sp0.x + 1.f / sp1.x)));
+      row[hi * RS + 2] = mk;
     }
+    for (int k = hi - 1; k >= lo; k--) {
+      mk = fmaf(-splq[k].w, mk, row[k * RS + 2]);
+      row[k * RS + 2] = mk;
+    }
+    const float m1 = row[RS + 2], m2 = row[2 * RS + 2];
+    row[2] = (wa == 0) ? m1 - (splq[1].x / splq[0].x) * (m2 - m1) : m1;
+    const float me = row[(Wn - 2) * RS + 2], me2 = row[(Wn - 3) * RS + 2];
+    row[(Wn - 1) * RS + 2] = (wb == n - 1) ? me + (splq[Wn - 3].x / splq[Wn - 2].x) * (me - me2) : me;
   }
   __syncthreads();
 
@@ -315,24 +334,25 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   const int npairs = nd >> 1;
   const float2* __restrict__ calq = P.calq;
   const float2 scale2 = f2(MATM_CAL_SCALE, MATM_CAL_SCALE), magic2 = f2(12582912.f, 12582912.f);
-  for (int64_t jb = j0 + tid; jb < j1; jb += F32_THREADS * F32_S) {
+  // warps start on multiples of 32 samples: a warp's store is then one 128-byte line per row whenever n_t % 32 == 0
+  for (int64_t jb = (j0 & ~(int64_t)31) + tid; jb < j1; jb += F32_THREADS * F32_S) {
     float a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
     const float4* yk[F32_S];
     int jq[F32_S];
 #pragma unroll
     for (int q = 0; q < F32_S; q++) {
-      // a sample index past the tile repeats the tile's last sample: the same value is stored to the same address by
+      // a sample index outside the tile repeats the tile's first / last sample: the same value is stored to the same address by
       // the thread that owns it, which is harmless and keeps the inner loop free of predicates
-      const int64_t j = min(jb + q * F32_THREADS, j1 - 1);
+      const int64_t j = max(min(jb + q * F32_THREADS, j1 - 1), j0);
       const double tj = P.t_full[j];
       int i = (int)floor((tj - t_atm0) * inv_ts);
       i = min(max(i, k0), k1 - 1);
       const int li = i - wa;
-      const float s = (float)(tj - P.t_atm[i]) * (spl[5 * li] * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
-      const float h26 = spl[5 * li + 1], c = 1.f - s;
+      const float s = (float)(tj - P.t_atm[i]) * (splq[li].x * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
+      const float hh = h26[li], c = 1.f - s;
       a1[q] = s;
-      a2[q] = h26 * (c * c * c - c);
-      a3[q] = h26 * (s * s * s - s);
+      a2[q] = hh * (c * c * c - c);
+      a3[q] = hh * (s * s * s - s);
       se[q] = ce[q] = 0.f;
       if (krj) {
         const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
