@@ -283,44 +283,82 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   }
   __syncthreads();
 
-  // ---- phase 2: second derivatives M_k of the not-a-knot cubic spline through the window's knots; warp 0, lane = detector.
+  // ---- phase 2: second derivatives M_k of the not-a-knot cubic spline through the window's knots; lane = detector.
   // Rows of the global tridiagonal system, swept with the global elimination factors.  At a true end of the series the
   // sweep starts / ends exactly; at an artificial end it starts from the locally-constant guess M = d / (a + b + c),
-  // whose error decays by (2 - sqrt 3) per knot across the halo.
-  if (warp == 0) {
+  // whose error decays by (2 - sqrt 3) per knot.  The same trick splits the window between the 8 warps: every warp
+  // sweeps its own segment of rows plus F32_HALO rows of run-in on either side, so the serial chain is ~40 rows instead
+  // of ~300 and no warp idles at the barrier for long.
+  {
     float* row = ymf + (lane >> 1) * 4 + (lane & 1);
     constexpr int RS = F32_NP * 4;  // stride between knots, in floats
-    const int lo = 1, hi = Wn - 2;
-    float y0 = row[0], y1 = row[RS], y2 = row[2 * RS];
-    float4 sp0 = splq[0], sp1 = splq[1];
+    constexpr int NW = F32_THREADS / 32;
+    const int lo = 1, hi = Wn - 2, nrows = hi - lo + 1;
+    const int ka = lo + (nrows * warp) / NW, kb = lo + (nrows * (warp + 1)) / NW - 1;  // this warp's rows [ka, kb]
     auto rhs3 = [](float ya, float yb, float yc, float iha, float ihb) { return 6.f * ((yc - yb) * ihb - (yb - ya) * iha); };
-    const float r_lo = rhs3(y0, y1, y2, sp0.x, sp1.x);
-    float dp = (wa == 0) ? r_lo * sp1.y : r_lo / (3.f * (1.f / sp0.x + 1.f / sp1.x)) * (1.f + sp1.w);
-    row[lo * RS + 2] = dp;
-    float r_k = r_lo;
-    for (int k = lo + 1; k <= hi; k++) {
-      y0 = y1;
-      y1 = y2;
-      y2 = row[(k + 1) * RS];
-      sp0 = sp1;
-      sp1 = splq[k];
-      r_k = rhs3(y0, y1, y2, sp0.x, sp1.x);
-      dp = fmaf(r_k, sp1.y, -sp1.z * dp);
-      row[k * RS + 2] = dp;
+    auto guess_at = [&](int k) {  // locally-constant estimate of M_k
+      const float iha = splq[k - 1].x, ihb = splq[k].x;
+      return rhs3(row[(k - 1) * RS], row[k * RS], row[(k + 1) * RS], iha, ihb) / (3.f * (1.f / iha + 1.f / ihb));
+    };
+    float dh[F32_HALO];  // forward-eliminated right-hand sides of the rows just above this warp's segment
+    if (ka <= kb) {
+      // forward elimination from fs (run-in) to kb; only this warp's rows are stored
+      const int fs = max(lo, ka - F32_HALO);
+      float y0 = row[(fs - 1) * RS], y1 = row[fs * RS], y2 = row[(fs + 1) * RS];
+      float4 sp0 = splq[fs - 1], sp1 = splq[fs];
+      const float r0 = rhs3(y0, y1, y2, sp0.x, sp1.x);
+      float dp = (fs == lo && wa == 0) ? r0 * sp1.y : r0 / (3.f * (1.f / sp0.x + 1.f / sp1.x)) * (1.f + sp1.w);
+      if (fs >= ka) row[fs * RS + 2] = dp;
+      for (int k = fs + 1; k <= kb; k++) {
+        y0 = y1;
+        y1 = y2;
+        y2 = row[(k + 1) * RS];
+        sp0 = sp1;
+        sp1 = splq[k];
+        dp = fmaf(rhs3(y0, y1, y2, sp0.x, sp1.x), sp1.y, -sp1.z * dp);
+        if (k >= ka) row[k * RS + 2] = dp;
+      }
     }
-    float mk = dp;  // M at hi
-    if (wb != n - 1) {
-      mk -= sp1.w * (r_k / (3.f * (1.f / sp0.x + 1.f / sp1.x)));
-      row[hi * RS + 2] = mk;
+    __syncthreads();
+    const int be = min(hi, kb + F32_HALO);  // back substitution starts here
+    if (ka <= kb) {
+#pragma unroll
+      for (int i = 0; i < F32_HALO; i++) dh[i] = (kb + 1 + i <= be) ? row[(kb + 1 + i) * RS + 2] : 0.f;
     }
-    for (int k = hi - 1; k >= lo; k--) {
-      mk = fmaf(-splq[k].w, mk, row[k * RS + 2]);
-      row[k * RS + 2] = mk;
+    __syncthreads();
+    if (ka <= kb) {
+      // M just above the segment: exact at the true end of the series, otherwise from the guess one row further up
+      float mk;
+      if (be == kb) {  // the segment ends at the last row of the window
+        mk = row[kb * RS + 2];
+        if (wb != n - 1) mk -= splq[kb].w * guess_at(kb);
+      } else {
+        mk = 0.f;
+        const bool true_end = be == hi && wb == n - 1;
+#pragma unroll
+        for (int i = F32_HALO - 1; i >= 0; i--) {
+          const int k = kb + 1 + i;
+          if (k == be)
+            mk = true_end ? dh[i] : dh[i] - splq[k].w * guess_at(k);
+          else if (k < be)
+            mk = fmaf(-splq[k].w, mk, dh[i]);
+        }
+        mk = fmaf(-splq[kb].w, mk, row[kb * RS + 2]);
+      }
+      row[kb * RS + 2] = mk;
+      for (int k = kb - 1; k >= ka; k--) {
+        mk = fmaf(-splq[k].w, mk, row[k * RS + 2]);
+        row[k * RS + 2] = mk;
+      }
     }
-    const float m1 = row[RS + 2], m2 = row[2 * RS + 2];
-    row[2] = (wa == 0) ? m1 - (splq[1].x / splq[0].x) * (m2 - m1) : m1;
-    const float me = row[(Wn - 2) * RS + 2], me2 = row[(Wn - 3) * RS + 2];
-    row[(Wn - 1) * RS + 2] = (wb == n - 1) ? me + (splq[Wn - 3].x / splq[Wn - 2].x) * (me - me2) : me;
+    __syncthreads();
+    if (warp == 0) {
+      const float m1 = row[RS + 2], m2 = row[2 * RS + 2];
+      row[2] = (wa == 0) ? m1 - (splq[1].x / splq[0].x) * (m2 - m1) : m1;
+    } else if (warp == 1) {
+      const float me = row[(Wn - 2) * RS + 2], me2 = row[(Wn - 3) * RS + 2];
+      row[(Wn - 1) * RS + 2] = (wb == n - 1) ? me + (splq[Wn - 3].x / splq[Wn - 2].x) * (me - me2) : me;
+    }
   }
   __syncthreads();
 
