@@ -293,8 +293,16 @@ def run_b200(args):
     alg_bytes = 4 * n_det * n_t + layer_bytes + 16 * n_atm + 8 * n_t + 16 * n_det
     peak, peak_src = measured_peak_gbs()
     achieved = alg_bytes / (synth_ms * 1e-3) / 1e9
+    traffic = None  # DRAM bytes of one launch from the committed ncu capture of this very workload, else null
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)["synth_f32_kernel"]
+        if t["n_det"] == n_det and t["n_t"] == n_t:
+            traffic = t["traffic"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": "synth_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
                 "kernel_ms": synth_ms, "step_ms_outside_kernel": ms_per_step - synth_ms}
 
     # ---- end to end through the public API with HOST buffers ----

@@ -94,6 +94,11 @@ int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_host, double 
  * pwv0 = weather.pwv (atmosphere.py:309).  Synchronises. */
 int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_desc* layers_host, double pwv0);
 
+/* Re-points the sampler at another set of smoothed-layer buffers of the same shapes (double buffering: the next
+ * realisation is beam-smoothed into the spare set while a synthesis kernel still reads the current one).  Host-side
+ * only: kernels launched afterwards see the new pointers; does not synchronise. */
+int matm_set_layer_data(matm_handle* h, int n_layers, const void* const* data_dev);
+
 /* Detectors: offsets_atm (n_det, 2) are the offsets the atmosphere uses (atmosphere.py:102-105), offsets_full
  * (n_det, 2) the roll-rotated offsets of obs.coords (observation.py:55-58) used by TOD.to for the elevation;
  * band_index (n_det,) int32; mueller00 (n_det,) = M[0,0] (array.py:204-218); gain (n_det,) = exp(gain_error*N(0,1))

@@ -38,6 +38,7 @@ SIGNATURES = {
     "matm_smooth_layer": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, vp, vp, vp]),
     "matm_set_scan": (C.c_int, [vp, C.c_int, c_dp, C.c_double, c_dp, c_dp, C.c_int64, c_dp, c_dp, c_dp]),
     "matm_set_layers": (C.c_int, [vp, C.c_int, C.POINTER(LayerDesc), C.c_double]),
+    "matm_set_layer_data": (C.c_int, [vp, C.c_int, C.POINTER(vp)]),
     "matm_set_detectors": (C.c_int, [vp, C.c_int64, c_dp, c_dp, c_ip, c_dp, c_dp]),
     "matm_set_bands": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
                                  c_dp, C.c_double, C.c_double, C.c_double, c_dp]),

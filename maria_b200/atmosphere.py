@@ -256,6 +256,7 @@ class Atmosphere:
         self.pipeline_depth = max(1, int(pipeline_depth))  # realisations whose AR chains may be in flight at once
         self._initialized = False
         self._generated = False
+        self._layers_set_once = False
 
     def __repr__(self):
         return f"Atmosphere(model={self.model}, region={self.region}, pwv={self.weather.pwv:.3f} mm, device=cuda:{self.device})"
@@ -339,7 +340,9 @@ class Atmosphere:
         for p in self.processes.values():
             p.bind(self.ctx, self.pipeline_depth)
         self._pending_slots, self._issued = [], 0
-        self._layer_dev = {}
+        self._layer_sets = [{}, {}]   # two sets of smoothed-layer buffers: the sampler reads one, the next is written
+        self._layer_cur = 0
+        self._reader_done = [None, None]  # event after the last kernel that reads each set
 
     def _bind_scan_and_detectors(self, obs, gain):
         """Host -> device: boresight at both rates, knot times, detector offsets / band index / Mueller / gain."""
@@ -433,23 +436,32 @@ class Atmosphere:
         ctx = self.ctx
         tc = ctx.torch
         cur = tc.cuda.current_stream(ctx.device)
-        readers_done = cur.record_event()
+        # the spare set of layer buffers: free once the kernels that read it (two realisations ago) are done, so the
+        # smoothing runs underneath the synthesis that still reads the current set
+        target = 1 - self._layer_cur if self._layers_set_once else self._layer_cur
+        readers_done = self._reader_done[target]
         slot = self._pending_slots.pop(0)
         for k, process in self.processes.items():
             stream = self._streams[(slot, k)]
-            stream.wait_event(readers_done)
+            if readers_done is not None:
+                stream.wait_event(readers_done)
             process._slot = slot
             process._values_host = None
             with tc.cuda.stream(stream):
                 st = ctx.stream_ptr()
                 for (li, col0, n_cols, sig_e, sig_x) in self._layer_plan[k]:
-                    out, scratch = self._layer_dev[li]
+                    out, scratch = self._layer_sets[target][li]
                     ctx.check(ctx.lib.matm_smooth_layer(ctx.h, process.values_device.data_ptr(), process.n_extrusion,
                                                         process.n_cross_section, col0, n_cols, sig_e, sig_x,
                                                         out.data_ptr(), scratch.data_ptr(), st))
             cur.wait_stream(stream)
+        self._layer_cur = target
         if not getattr(self, "_layers_set", False):
             self.set_layers()
+        else:
+            ptrs = (C.c_void_p * len(self._layer_order))(*[self._layer_sets[target][li][0].data_ptr() for li in self._layer_order])
+            ctx.check(ctx.lib.matm_set_layer_data(ctx.h, len(self._layer_order), ptrs))
+        self._layers_set_once = True
         self._generated = True
 
     def drain(self):
@@ -475,21 +487,23 @@ class Atmosphere:
                 col0, n_cols = int(cols[0]), len(cols)
                 beam_sigma = host.gaussian_beam_physical_fwhm(dets.primary_size, L["z"][li], dets.band_center).mean() / 2.355
                 plan.append((int(li), col0, n_cols, float(beam_sigma / process.extrusion_res), float(beam_sigma / L["res"][li])))
-                self._layer_dev[int(li)] = (ctx.empty((process.n_extrusion, n_cols)),
-                                            ctx.empty((process.n_extrusion, n_cols), ctx.torch.float64))
+                for ls in self._layer_sets:
+                    ls[int(li)] = (ctx.empty((process.n_extrusion, n_cols)),
+                                   ctx.empty((process.n_extrusion, n_cols), ctx.torch.float64))
             self._layer_plan[k] = plan
 
     def set_layers(self):
         """Hand the layer geometry (height, transform, grids, wind) and the device layers to the sampler."""
         ctx, L = self.ctx, self.layers
         descs = (_lib.LayerDesc * len(L["h"]))()
-        keep, n_layers = [], 0
+        keep, n_layers, order = [], 0, []
         for k, process in self.processes.items():
             vx, vy = _lib.f64(process.vx), _lib.f64(process.vy)
             keep += [vx, vy]
             for (li, col0, n_cols, _, _) in self._layer_plan[k]:
                 d = descs[n_layers]
                 d.data_dev, d.n_ext, d.n_cs = self._layer_dev[li][0].data_ptr(), process.n_extrusion, n_cols
+                order.append(li)
                 d.h, d.pwv_rms = float(L["h"][li]), float(L["pwv_rms"][li])
                 d.transform = (C.c_double * 9)(*np.asarray(process.transform, dtype=float).ravel())
                 d.ext0, d.ext_step = float(process.extrusion[0]), float(process.extrusion_res)
@@ -498,7 +512,17 @@ class Atmosphere:
                 d.vx_host, d.vy_host = _lib.dptr(vx), _lib.dptr(vy)
                 n_layers += 1
         ctx.check(ctx.lib.matm_set_layers(ctx.h, n_layers, descs, float(self.weather.pwv)))
+        self._layer_order = order
         self._layers_set = True
+
+    @property
+    def _layer_dev(self):
+        """The set of smoothed-layer buffers the sampler currently reads."""
+        return self._layer_sets[self._layer_cur]
+
+    def _mark_readers(self):
+        """Record that a kernel reading the current layer set has just been enqueued on the current stream."""
+        self._reader_done[self._layer_cur] = self.ctx.torch.cuda.current_stream(self.ctx.device).record_event()
 
     def smoothed_layer(self, li):
         """Beam-smoothed layer ``li`` as a host array (validation helper)."""
@@ -510,6 +534,7 @@ class Atmosphere:
         n_det = self._obs.instrument.dets.n - det0 if n_det is None else n_det
         out = ctx.empty((n_det, len(self.boresight.t)), ctx.torch.float64)
         ctx.check(ctx.lib.matm_zenith_pwv(ctx.h, det0, n_det, out.data_ptr(), ctx.stream_ptr()))
+        self._mark_readers()
         return out
 
     def synthesize(self, det0=0, n_det=None, units="K_RJ", apply_gain=True, out=None):
@@ -520,6 +545,7 @@ class Atmosphere:
             out = ctx.empty((n_det, len(self._obs.boresight.t)))
         ctx.check(ctx.lib.matm_synthesize(ctx.h, det0, n_det, out.data_ptr(), _lib.UNITS_KRJ if units == "K_RJ" else _lib.UNITS_PW,
                                           1 if apply_gain else 0, ctx.stream_ptr()))
+        self._mark_readers()
         return out
 
     def synthesize_host(self, out_host, det0=0, n_det=None, units="K_RJ", apply_gain=True):

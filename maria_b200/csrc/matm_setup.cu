@@ -243,6 +243,16 @@ __global__ void det_kernel(const double* __restrict__ off_atm, const double* __r
   }
 }
 
+extern "C" int matm_set_layer_data(matm_handle* h, int n_layers, const void* const* data_dev) {
+  MATM_CHECK_HANDLE(h);
+  if (!h->have_layers) MATM_FAIL_ARG(h, "matm_set_layer_data: call matm_set_layers first");
+  if (n_layers != h->P.n_layers || !data_dev) MATM_FAIL_ARG(h, "matm_set_layer_data: layer count does not match matm_set_layers");
+  for (int l = 0; l < n_layers; l++)
+    if (!data_dev[l]) MATM_FAIL_ARG(h, "matm_set_layer_data: null layer pointer");
+  for (int l = 0; l < n_layers; l++) h->P.layers[l].data = data_dev[l];
+  return MATM_OK;
+}
+
 extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* offsets_atm_host,
                                   const double* offsets_full_host, const int32_t* band_index_host,
                                   const double* mueller00_host, const double* gain_host) {
