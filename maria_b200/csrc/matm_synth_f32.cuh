@@ -55,7 +55,7 @@ __device__ __forceinline__ float fast_rcp(float x) {
 __device__ __forceinline__ void st_row(float* row, int j, float v) {
   float* a;
   asm("mad.wide.s32 %0, %1, 4, %2;" : "=l"(a) : "r"(j), "l"(row));
-  asm volatile("st.global.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
+  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
 }
 // asin on [-1, 1]: pi/2 - sqrt(1 - |x|) P7(|x|)  (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 rad)
 __device__ __forceinline__ float fast_asin(float x) {
