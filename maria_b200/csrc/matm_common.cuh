@@ -94,6 +94,7 @@ struct matm_handle {
   std::map<std::pair<int64_t, int64_t>, int32_t*> det_order;
   int* flags = nullptr;
   std::vector<double> az_atm_host, el_atm_host;
+  int64_t min_samples_per_interval = 0;  // over the interior spline intervals (decides the 4-samples-per-thread path)
   // e2e staging
   void* stage_dev[2] = {nullptr, nullptr};
   void* stage_pinned[2] = {nullptr, nullptr};

@@ -142,6 +142,13 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_ho
   P.bore_full = h->bore_full;
   P.t_full = h->t_full;
   P.jstart = h->jstart;
+  {
+    std::vector<int64_t> js((size_t)n_t_atm + 1);
+    MATM_CUDA(h, cudaMemcpy(js.data(), h->jstart, js.size() * sizeof(int64_t), cudaMemcpyDeviceToHost));
+    int64_t mn = INT64_MAX;
+    for (int k = 1; k + 2 < n_t_atm; k++) mn = std::min(mn, js[k + 1] - js[k]);  // interior intervals only
+    h->min_samples_per_interval = mn == INT64_MAX ? 0 : mn;
+  }
   P.t_atm = h->t_atm;
   P.spl = h->spl;
   h->have_scan = true;

@@ -1,0 +1,159 @@
+"""GPU parity tests on the BASELINE.json configurations (maria_b200/configs.py).
+
+C1 runs at its full size end to end against the oracle.  C2 / C3 keep their scan, bands and layer geometry and thin the
+focal plane so that the oracle finishes in seconds.  C4 keeps the full 1-hour time axis and the full-size layers
+(n_ext up to 18 684, 37 k recurrence steps): the AR recurrence is checked against the oracle with identical host
+noise, and the detector x time stages against the oracle fed with the device's own layers, for a subset of detectors
+spread over the whole focal plane.  Size-independent properties (gain linearity, unit round trip, shard bit-equality,
+determinism) are checked on the device at C4 geometry.
+
+Tolerances: fp64 path 1e-10 relative; fp32 path 2e-6 on the total TOD and 5e-4 on its fluctuating part.
+"""
+import numpy as np
+import pytest
+
+import maria_b200 as M
+from common import relmax
+from maria_b200 import configs
+from maria_b200 import inputs as I
+from oracle import atm_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+TOL64, TOL32_TOTAL, TOL32_FLUCT = 1e-10, 2e-6, 5e-4
+
+
+def _device(cfg, dtype, seed, **akw):
+    np.random.seed(seed)
+    sim = M.Simulation(cfg["instrument"], cfg["plan"], cfg["site"], atmosphere="2d", dtype=dtype,
+                       atmosphere_kwargs=dict(weather=cfg["weather"], spectrum=cfg["spectrum"], **akw))
+    return sim
+
+
+def _oracle(cfg, seed):
+    np.random.seed(seed)
+    return O.simulate(cfg["instrument"], cfg["plan"], cfg["site"], cfg["weather"], cfg["spectrum"], np.random,
+                      dtype=np.float64)
+
+
+def _check32(dev, ref):
+    assert relmax(dev, ref) < TOL32_TOTAL
+    mean = ref.mean(axis=1, keepdims=True)
+    fl_ref, fl_dev = ref - mean, np.asarray(dev, dtype=np.float64) - mean
+    assert np.max(np.abs(fl_dev - fl_ref)) / np.max(np.abs(fl_ref)) < TOL32_FLUCT
+
+
+@pytest.mark.parametrize("name, kwargs", [
+    ("c1", {}),                                         # MUSTANG-2 daisy, full size: 217 detectors x 30 000 samples
+    ("c2", dict(n_per_array=24, duration=120.0)),       # ACT-like CES, 3 bands x 2 polarisations, 200 Hz
+    ("c3", dict(n_det=180, duration=200.0, pwv=0.5)),   # 3-band array, PWV through the weather override
+    ("c3", dict(n_det=90, duration=100.0, pwv=2.0)),
+])
+def test_baseline_config_matches_oracle(cuda, name, kwargs):
+    cfg = configs.CONFIGS[name](**kwargs)
+    ref = _oracle(cfg, seed=17)["tod_K_RJ"]
+    tod64 = _device(cfg, np.float64, 17, geometry="exact").run(units="K_RJ")[0].data["atmosphere"]
+    assert tod64.shape == ref.shape and relmax(tod64, ref) < TOL64
+    tod32 = _device(cfg, np.float32, 17, geometry="exact").run(units="K_RJ")[0].data["atmosphere"]
+    assert tod32.dtype == np.float32
+    _check32(tod32, ref)
+
+
+# ---- C4 geometry: full time axis, full-size layers ---------------------------------------------------------------
+@pytest.fixture(scope="module")
+def c4():
+    return configs.c4_atlast(n_det=2048, duration=3600.0, sample_rate=50.0)
+
+
+def _oracle_with_layers(cfg, atm, sel, layer_values):
+    """Oracle stages a6-a14 for the detectors ``sel``, with the layer values given (the device's own realisation)."""
+    dets = cfg["instrument"].dets
+    sub = I.Array(dets.xi[sel], dets.eta[sel], dets.band_name[sel], [b for b in dets.bands if b.name in set(dets.band_name[sel])],
+                  dets.gamma[sel], dets.primary_size[sel])
+    # the beam smoothing uses the mean beam of the WHOLE array (atmosphere.py:328-339): keep it
+    geo = {k: dict(cross_section=p.cross_section, extrusion=p.extrusion, A=p.A, B=p.B, transform=p.transform, vx=p.vx, vy=p.vy,
+                   layer_index=p.layer_index, labels=p.labels, extrusion_res=p.extrusion_res) for k, p in atm.processes.items()}
+    o_obs = O.Observation(I.Instrument(sub, name="subset"), cfg["plan"], cfg["site"])
+    o_atm = O.atmosphere_from_geometry(cfg["weather"], cfg["spectrum"], atm.layers, atm.timestep, atm.boresight.t,
+                                       atm.boresight.az, atm.boresight.el, sub.offsets, geo)
+    for k, p in o_atm.processes.items():
+        vals = np.array(layer_values[k])
+        p.run = (lambda rng, record=None, _v=vals, _p=p: setattr(_p, "values", _v))
+
+    class Zeros:  # gain_error = exp(g * 0) = 1
+        def standard_normal(self, size=None):
+            return np.zeros(size)
+
+    full = cfg["instrument"]  # beam smoothing width from the full array
+    o_atm_sim = o_atm.simulate_pwv
+    o_atm.simulate_pwv = lambda instrument, rng, record=None: o_atm_sim(full, rng, record=record)
+    loading, meta = O.run_obs(o_obs, o_atm, Zeros(), dtype=np.float64)
+    return O.tod_to_K_RJ(loading, o_obs, o_atm, meta, out_dtype=np.float64)
+
+
+def test_c4_full_length_recurrence_matches_oracle(cuda, c4):
+    """a5 at C4's layer sizes: 2 x 18 684 dependent steps, identical host noise, float64: device chain == oracle chain."""
+    sim = _device(c4, np.float64, 23, noise="host", geometry="fast")
+    atm = sim.obs_list[0].atmosphere
+    k = max(atm.processes, key=lambda q: atm.processes[q].n_extrusion * atm.processes[q].n_cross_section)
+    p = atm.processes[k]
+    assert p.n_extrusion > 15000 and p.n_cross_section > 100
+    rng = np.random.default_rng(5)
+    buffer0 = rng.standard_normal((3 * p.n_extrusion, p.n_cross_section))
+    z = rng.standard_normal((2 * p.n_extrusion, p.n_cross_section))
+    dev = p.run(rng=O.ReplayRNG([buffer0, z])).cpu().numpy()
+    q = O.AutoregressiveProcess(p.cross_section, p.extrusion, {}, jitter=1e-8)
+    q.A, q.B = p.A, p.B
+    ref = q.run(O.ReplayRNG([buffer0] + [z[i] for i in range(len(z))]))
+    assert relmax(dev, ref) < TOL64
+
+
+def test_c4_full_time_axis_matches_oracle(cuda, c4):
+    """a6-a14 on the 1-hour raster (7950 knots -> 180 000 samples) with the production Philox layers: the float32 and the
+    float64 device paths against the oracle fed with the device's layers, detectors spread over the 2-degree field."""
+    n = c4["instrument"].dets.n
+    sel = np.unique(np.linspace(0, n - 1, 24).astype(int))
+    out = {}
+    for dtype in (np.float64, np.float32):
+        sim = _device(c4, dtype, 23, noise="philox", seed=77, geometry="fast")
+        obs, atm = sim.obs_list[0], sim.obs_list[0].atmosphere
+        atm.simulate_pwv()
+        atm.set_gain(np.ones(n))
+        tod = sim._compute_atmospheric_loading(obs, units="K_RJ", apply_gain=True)
+        atm.check_flags()
+        out[dtype] = tod[sel].cpu().numpy()
+        if dtype is np.float64:
+            layers = {k: p.values for k, p in atm.processes.items()}
+            ref = _oracle_with_layers(c4, atm, sel, layers)
+    assert out[np.float64].shape == ref.shape == (len(sel), 180000)
+    assert relmax(out[np.float64], ref) < TOL64
+    _check32(out[np.float32], ref)
+
+
+def test_c4_properties_on_device(cuda, c4):
+    """Gain linearity, pW <-> K_RJ round trip, shard bit-equality with ragged boundaries, determinism; float32."""
+    n = c4["instrument"].dets.n
+    sim = _device(c4, np.float32, 23, noise="philox", seed=3, geometry="fast")
+    obs, atm = sim.obs_list[0], sim.obs_list[0].atmosphere
+    atm.simulate_pwv()
+    rng = np.random.default_rng(1)
+    gain = np.exp(0.05 * rng.standard_normal(n))
+    atm.set_gain(gain)
+    krj = sim._compute_atmospheric_loading(obs, units="K_RJ", apply_gain=True)
+    again = sim._compute_atmospheric_loading(obs, units="K_RJ", apply_gain=True)
+    assert cuda.equal(krj, again)  # deterministic
+    nogain = sim._compute_atmospheric_loading(obs, units="K_RJ", apply_gain=False)
+    ratio = (krj[::37, ::997] / nogain[::37, ::997]).cpu().numpy()
+    assert np.max(np.abs(ratio / gain[::37, None] - 1)) < 1e-6  # linear in the detector gain
+    # ragged shards: 1 detector, an odd count, a tile-straddling range; every shard equals the full run bit for bit
+    for d0, m in [(0, 1), (5, 33), (1000, 531), (n - 7, 7)]:
+        part = sim._compute_atmospheric_loading(obs, d0, m, units="K_RJ", apply_gain=True)
+        assert cuda.equal(part, krj[d0:d0 + m]), (d0, m)
+    # units: pW -> K_RJ -> pW on the device equals the pW synthesis (tests/tod/test_tod.py:37-49 round trip)
+    pw = sim._compute_atmospheric_loading(obs, 0, 256, units="pW", apply_gain=True)
+    tod = M.TOD({"atmosphere": krj[:256].clone()}, dets=obs.instrument.dets, coords=obs.coords, units="K_RJ", dtype=np.float32,
+                metadata={"det0": 0}, calibrator=atm)
+    back = tod.to("pW").device_data["atmosphere"]
+    assert float((back / pw - 1).abs().max()) < 2e-6
+    assert bool(cuda.isfinite(krj).all())
+    atm.check_flags()
