@@ -23,8 +23,8 @@ pytestmark = pytest.mark.gpu
 TOL64, TOL32_TOTAL, TOL32_FLUCT = 1e-10, 2e-6, 5e-4
 
 
-def _device(cfg, dtype, seed, **akw):
-    np.random.seed(seed)
+def _device(cfg, dtype, np_seed, **akw):
+    np.random.seed(np_seed)
     sim = M.Simulation(cfg["instrument"], cfg["plan"], cfg["site"], atmosphere="2d", dtype=dtype,
                        atmosphere_kwargs=dict(weather=cfg["weather"], spectrum=cfg["spectrum"], **akw))
     return sim
