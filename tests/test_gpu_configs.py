@@ -157,3 +157,76 @@ def test_c4_properties_on_device(cuda, c4):
     assert float((back / pw - 1).abs().max()) < 2e-6
     assert bool(cuda.isfinite(krj).all())
     atm.check_flags()
+
+
+def test_c5_six_hour_scan_runs_and_matches_oracle_subset(cuda):
+    """C5's time axis (6 h at 50 Hz = 1.08 M samples per detector, ~48 k knots, layers six times longer than C4's) on a
+    thinned focal plane: the float32 path against the oracle fed with the device's layers, and no line of sight leaves a
+    layer over the whole scan."""
+    cfg = configs.c5_long(n_det=256, duration=21600.0, sample_rate=50.0)
+    n = cfg["instrument"].dets.n
+    sim = _device(cfg, np.float32, 29, noise="philox", seed=11, geometry="fast")
+    obs, atm = sim.obs_list[0], sim.obs_list[0].atmosphere
+    assert max(p.n_extrusion for p in atm.processes.values()) > 80000
+    atm.simulate_pwv()
+    atm.set_gain(np.ones(n))
+    tod = sim._compute_atmospheric_loading(obs, units="K_RJ", apply_gain=True)
+    assert atm.check_flags() == 0
+    assert tod.shape == (n, 1080000) and bool(cuda.isfinite(tod).all())
+    sel = np.array([0, n // 3, n - 1])
+    ref = _oracle_with_layers(cfg, atm, sel, {k: p.values for k, p in atm.processes.items()})
+    _check32(tod[sel].cpu().numpy(), ref)
+
+
+def _log_binned_psd(x, rate, n_bins=12):
+    """Hann-windowed, linearly detrended periodogram, log-binned (the recipe of maria/plotting/tod.py:100-112)."""
+    n = x.shape[-1]
+    t = np.arange(n)
+    x = x - np.polyval(np.polyfit(t, x.T, 1), t[:, None]).T if x.ndim > 1 else x - np.polyval(np.polyfit(t, x, 1), t)
+    w = np.hanning(n)
+    ps = np.abs(np.fft.rfft(x * w, axis=-1)) ** 2 / (rate * np.sum(w**2))
+    f = np.fft.rfftfreq(n, 1 / rate)
+    edges = np.geomspace(f[1], f[-1], n_bins + 1)
+    idx = np.clip(np.digitize(f[1:], edges) - 1, 0, n_bins - 1)
+    return np.array([ps[..., 1:][..., idx == b].mean() for b in range(n_bins)])
+
+
+def test_philox_tod_power_spectrum_matches_oracle_realisations(cuda):
+    """Production RNG, statistical check: the log-binned power spectrum of the device TOD over many
+    Philox seeds agrees with that of oracle realisations drawn from numpy's generator, within sampling error."""
+    cfg = configs.c3_multiband(n_det=24, duration=120.0, sample_rate=20.0)
+    np.random.seed(31)
+    sim = M.Simulation(cfg["instrument"], cfg["plan"], cfg["site"], atmosphere="2d", dtype=np.float32,
+                       atmosphere_kwargs=dict(weather=cfg["weather"], spectrum=cfg["spectrum"], noise="philox", seed=1,
+                                              geometry="exact"))
+    obs, atm = sim.obs_list[0], sim.obs_list[0].atmosphere
+    n = cfg["instrument"].dets.n
+    atm.set_gain(np.ones(n))
+    n_real = 48
+    dev = []
+    for s in range(n_real):
+        atm.seed = 100 + s
+        atm.simulate_pwv()
+        dev.append(_log_binned_psd(sim._compute_atmospheric_loading(obs, units="K_RJ", apply_gain=True).cpu().numpy().astype(float), 20.0))
+    # oracle realisations on the same geometry (same A, B, transforms), independent noise
+    geo = {k: dict(cross_section=p.cross_section, extrusion=p.extrusion, A=p.A, B=p.B, transform=p.transform, vx=p.vx, vy=p.vy,
+                   layer_index=p.layer_index, labels=p.labels, extrusion_res=p.extrusion_res) for k, p in atm.processes.items()}
+    o_obs = O.Observation(cfg["instrument"], cfg["plan"], cfg["site"])
+    o_atm = O.atmosphere_from_geometry(cfg["weather"], cfg["spectrum"], atm.layers, atm.timestep, atm.boresight.t,
+                                       atm.boresight.az, atm.boresight.el, cfg["instrument"].dets.offsets, geo)
+    rng = np.random.default_rng(7)
+
+    class NoGain:
+        def standard_normal(self, size=None):
+            return rng.standard_normal(size) if np.ndim(size) or (size or 0) != n else np.zeros(n)
+
+    ref = []
+    for s in range(n_real):
+        loading, meta = O.run_obs(o_obs, o_atm, NoGain(), dtype=np.float64)
+        ref.append(_log_binned_psd(O.tod_to_K_RJ(loading, o_obs, o_atm, meta, out_dtype=np.float64), 20.0))
+    dev, ref = np.array(dev), np.array(ref)
+    ratio = dev.mean(axis=0) / ref.mean(axis=0)
+    # the propagator is close to a unit root, so single realisations scatter by factors; 48 realisations each side bring the
+    # ratio of the means within ~40 % per bin
+    err = np.sqrt((dev.std(axis=0) / dev.mean(axis=0)) ** 2 + (ref.std(axis=0) / ref.mean(axis=0)) ** 2) / np.sqrt(n_real)
+    assert np.all(np.abs(np.log(ratio)) < np.maximum(5 * err, 0.4)), (ratio, err)
