@@ -90,8 +90,12 @@ struct matm_handle {
   int* calq_kind = nullptr;
   float4* calq_aux = nullptr;
   // processing order of the detectors of a requested range (spatially coherent tiles; matm_detector_order)
-  std::vector<float> det_xy_host;  // (n_det, 2) the atmosphere's offsets, kept for the ordering
-  std::map<std::pair<int64_t, int64_t>, int32_t*> det_order;
+  std::vector<double> det_xy_host;  // (n_det, 2) the atmosphere's offsets, kept for the ordering
+  struct DetOrder {
+    int32_t* order;   // (n_det) absolute detector indices in processing order
+    uint8_t* tile_m;  // (n_tiles) 1, 2 or 4: the 32 detectors of the tile come in aligned groups of that many co-located ones
+  };
+  std::map<std::pair<int64_t, int64_t>, DetOrder> det_order;
   int* flags = nullptr;
   std::vector<double> az_atm_host, el_atm_host;
   int64_t min_samples_per_interval = 0;  // over the interior spline intervals (decides the 4-samples-per-thread path)
@@ -143,7 +147,7 @@ static inline int matm_upload(matm_handle* h, T** dst, const T* src_host, size_t
 // Device array of n_det absolute detector indices: the order in which the detectors of [det0, det0 + n_det) are
 // processed.  Consecutive entries are neighbours in the focal plane (Morton order of the offsets), so that the 32
 // detectors of a warp sample the same few cells of every layer whatever order the caller's array is in.
-int matm_detector_order(matm_handle* h, int64_t det0, int64_t n_det, const int32_t** order_dev);
+int matm_detector_order(matm_handle* h, int64_t det0, int64_t n_det, const int32_t** order_dev, const uint8_t** tile_m_dev);
 
 static inline int matm_set_device(matm_handle* h) {
   MATM_CUDA(h, cudaSetDevice(h->device));

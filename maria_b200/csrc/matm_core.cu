@@ -50,7 +50,10 @@ extern "C" int matm_destroy(matm_handle* h) {
   cudaFree(h->tabR);
   cudaFree(h->calq);
   cudaFree(h->calq_kind);
-  for (auto& kv : h->det_order) cudaFree(kv.second);
+  for (auto& kv : h->det_order) {
+    cudaFree(kv.second.order);
+    cudaFree(kv.second.tile_m);
+  }
   cudaFree(h->calq_aux);
   cudaFree(h->flags);
   for (int i = 0; i < 2; i++) {

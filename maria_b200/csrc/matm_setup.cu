@@ -289,8 +289,11 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   cudaFree(oa);
   cudaFree(of);
   h->det_xy_host.resize((size_t)n_det * 2);
-  for (size_t i = 0; i < (size_t)n_det * 2; i++) h->det_xy_host[i] = (float)offsets_atm_host[i];
-  for (auto& kv : h->det_order) cudaFree(kv.second);
+  for (size_t i = 0; i < (size_t)n_det * 2; i++) h->det_xy_host[i] = offsets_atm_host[i];
+  for (auto& kv : h->det_order) {
+    cudaFree(kv.second.order);
+    cudaFree(kv.second.tile_m);
+  }
   h->det_order.clear();
   SynthParams& P = h->P;
   P.n_det = n_det;
@@ -311,39 +314,72 @@ static inline uint32_t spread_bits16(uint32_t v) {  // 16 bits -> every other bi
   return v;
 }
 
-int matm_detector_order(matm_handle* h, int64_t det0, int64_t n_det, const int32_t** order_dev) {
+int matm_detector_order(matm_handle* h, int64_t det0, int64_t n_det, const int32_t** order_dev, const uint8_t** tile_m_dev) {
   const auto key = std::make_pair(det0, n_det);
   auto it = h->det_order.find(key);
   if (it != h->det_order.end()) {
-    *order_dev = it->second;
+    *order_dev = it->second.order;
+    *tile_m_dev = it->second.tile_m;
     return MATM_OK;
   }
   if (h->det_order.size() >= 256) {  // bounded cache (chunked delivery asks for a handful of ranges)
-    for (auto& kv : h->det_order) cudaFree(kv.second);
+    for (auto& kv : h->det_order) {
+      cudaFree(kv.second.order);
+      cudaFree(kv.second.tile_m);
+    }
     h->det_order.clear();
   }
-  const float* xy = h->det_xy_host.data() + 2 * (size_t)det0;
-  float lo[2] = {xy[0], xy[1]}, hi[2] = {xy[0], xy[1]};
+  const double* xy = h->det_xy_host.data() + 2 * (size_t)det0;
+  double lo[2] = {xy[0], xy[1]}, hi[2] = {xy[0], xy[1]};
   for (int64_t i = 0; i < n_det; i++)
     for (int a = 0; a < 2; a++) {
-      lo[a] = fminf(lo[a], xy[2 * i + a]);
-      hi[a] = fmaxf(hi[a], xy[2 * i + a]);
+      lo[a] = fmin(lo[a], xy[2 * i + a]);
+      hi[a] = fmax(hi[a], xy[2 * i + a]);
     }
-  const float span = fmaxf(fmaxf(hi[0] - lo[0], hi[1] - lo[1]), 1e-30f);
+  const double span = fmax(fmax(hi[0] - lo[0], hi[1] - lo[1]), 1e-300);
   std::vector<std::pair<uint32_t, int32_t>> keyed((size_t)n_det);
   for (int64_t i = 0; i < n_det; i++) {
-    const uint32_t qx = (uint32_t)fminf(65535.f, (xy[2 * i] - lo[0]) / span * 65535.f);
-    const uint32_t qy = (uint32_t)fminf(65535.f, (xy[2 * i + 1] - lo[1]) / span * 65535.f);
-    keyed[(size_t)i] = std::make_pair(spread_bits16(qx) | (spread_bits16(qy) << 1), (int32_t)(det0 + i));
+    const uint32_t qx = (uint32_t)fmin(65535.0, (xy[2 * i] - lo[0]) / span * 65535.0);
+    const uint32_t qy = (uint32_t)fmin(65535.0, (xy[2 * i + 1] - lo[1]) / span * 65535.0);
+    keyed[(size_t)i] = std::make_pair(spread_bits16(qx) | (spread_bits16(qy) << 1), (int32_t)i);
   }
-  std::sort(keyed.begin(), keyed.end());  // ties (co-located detectors of different bands) stay in index order
+  // Morton order; inside one Morton cell by exact position, so that co-located detectors always end up adjacent
+  std::sort(keyed.begin(), keyed.end(), [xy](const std::pair<uint32_t, int32_t>& a, const std::pair<uint32_t, int32_t>& b) {
+    if (a.first != b.first) return a.first < b.first;
+    const double ax = xy[2 * a.second], ay = xy[2 * a.second + 1], bx = xy[2 * b.second], by = xy[2 * b.second + 1];
+    if (ax != bx) return ax < bx;
+    if (ay != by) return ay < by;
+    return a.second < b.second;
+  });
   std::vector<int32_t> order((size_t)n_det);
-  for (int64_t i = 0; i < n_det; i++) order[(size_t)i] = keyed[(size_t)i].second;
-  int32_t* dev = nullptr;
-  MATM_CUDA(h, cudaMalloc((void**)&dev, (size_t)n_det * sizeof(int32_t)));
-  MATM_CUDA(h, cudaMemcpy(dev, order.data(), (size_t)n_det * sizeof(int32_t), cudaMemcpyHostToDevice));
-  h->det_order[key] = dev;
-  *order_dev = dev;
+  for (int64_t i = 0; i < n_det; i++) order[(size_t)i] = (int32_t)(det0 + keyed[(size_t)i].second);
+  // per tile of 32 slots: the largest M in {4, 2, 1} such that every aligned group of M slots shares one position
+  const int64_t n_tiles = (n_det + 31) / 32;
+  std::vector<uint8_t> tile_m((size_t)n_tiles, 1);
+  auto same = [&](int64_t s0, int64_t s1) {
+    const int32_t a = keyed[(size_t)s0].second, b = keyed[(size_t)s1].second;
+    return xy[2 * a] == xy[2 * b] && xy[2 * a + 1] == xy[2 * b + 1];
+  };
+  for (int64_t t = 0; t < n_tiles; t++) {
+    if ((t + 1) * 32 > n_det) continue;  // partial tile
+    for (int m = 4; m >= 2; m >>= 1) {
+      bool ok = true;
+      for (int g = 0; g < 32 && ok; g += m)
+        for (int j = 1; j < m && ok; j++) ok = same(t * 32 + g, t * 32 + g + j);
+      if (ok) {
+        tile_m[(size_t)t] = (uint8_t)m;
+        break;
+      }
+    }
+  }
+  matm_handle::DetOrder rec = {nullptr, nullptr};
+  MATM_CUDA(h, cudaMalloc((void**)&rec.order, (size_t)n_det * sizeof(int32_t)));
+  MATM_CUDA(h, cudaMemcpy(rec.order, order.data(), (size_t)n_det * sizeof(int32_t), cudaMemcpyHostToDevice));
+  MATM_CUDA(h, cudaMalloc((void**)&rec.tile_m, (size_t)n_tiles));
+  MATM_CUDA(h, cudaMemcpy(rec.tile_m, tile_m.data(), (size_t)n_tiles, cudaMemcpyHostToDevice));
+  h->det_order[key] = rec;
+  *order_dev = rec.order;
+  *tile_m_dev = rec.tile_m;
   return MATM_OK;
 }
 

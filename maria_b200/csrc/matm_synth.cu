@@ -297,11 +297,12 @@ static int launch_synth(matm_handle* h, int64_t det0, int64_t n_det, void* out_d
     const int64_t blocks = ((n_det + F32_DT - 1) / F32_DT) * n_ttiles;
     if (blocks > INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize: too many tiles; split the detector range");
     const int32_t* order = nullptr;
-    int rc = matm_detector_order(h, det0, n_det, &order);
+    const uint8_t* tile_m = nullptr;
+    int rc = matm_detector_order(h, det0, n_det, &order, &tile_m);
     if (rc) return rc;
     size_t smem = synth_f32_smem(P.n_layers);
     MATM_CUDA(h, cudaFuncSetAttribute(synth_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    synth_f32_kernel<<<(unsigned)blocks, F32_THREADS, smem, st>>>(P, order, det0, n_det, (float*)out_dev, units, apply_gain);
+    synth_f32_kernel<<<(unsigned)blocks, F32_THREADS, smem, st>>>(P, order, tile_m, det0, n_det, (float*)out_dev, units, apply_gain);
   } else {
     const int n_ttiles = (P.n_t_atm - 1 + Tile<float>::KT - 1) / Tile<float>::KT;
     const int64_t blocks = ((n_det + DT - 1) / DT) * n_ttiles;

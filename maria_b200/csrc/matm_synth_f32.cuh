@@ -89,118 +89,28 @@ __device__ __noinline__ float cal_factor_special(const SynthParams& P, int idx, 
   return 1.0f / den;
 }
 
-__global__ void __launch_bounds__(F32_THREADS, F32_MINB)
-    synth_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order, int64_t det0, int64_t n_det,
-                     float* __restrict__ out, int units, int apply_gain) {
-  extern __shared__ __align__(16) unsigned char dyn[];
-  float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_d0, y_d1, m_d0, m_d1}
-  float* ymf = reinterpret_cast<float*>(dyn);
-  float4* splq = ym4 + F32_W * F32_NP;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
-  float* h26 = reinterpret_cast<float*>(splq + F32_W);               // [W] h_k^2 / 6
-  Knot<float>* knots = reinterpret_cast<Knot<float>*>(reinterpret_cast<float*>(splq) + F32_SPLN);
-  LayerKnot<float>* lk = reinterpret_cast<LayerKnot<float>*>(knots + F32_W);  // [n_layers][W]
-  __shared__ __align__(16) LayerF ls[MATM_MAX_LAYERS];
-  __shared__ float4 dc_uw[F32_NP];  // {u_d0, u_d1, w_d0, w_d1} of the rolled offsets
-  __shared__ int2 dc_tab[F32_NP];   // calibration-table base of each detector's band, minus the rounding magic
-  __shared__ float dc_gain[F32_DT];
-  __shared__ int dc_band[F32_DT];
-  __shared__ __align__(16) long long dc_row[F32_DT];  // element offset of each detector's output row
-
-  const int n = P.n_t_atm;
-  const int n_int = n - 1;
-  const int n_layers = P.n_layers;
-  const int n_ttiles = (n_int + F32_KT - 1) / F32_KT;
-  const int64_t dtile = blockIdx.x / n_ttiles;
-  const int ttile = blockIdx.x % n_ttiles;
-  const int k0 = ttile * F32_KT, k1 = min(k0 + F32_KT, n_int);
-  const int wa = max(0, k0 - F32_HALO), wb = min(n - 1, k1 + F32_HALO);
-  const int Wn = wb - wa + 1;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int64_t dbase = dtile * F32_DT;
-  const int nd = (int)min((int64_t)F32_DT, n_det - dbase);
-  constexpr int MAGIC_BITS = 0x4B400000;  // bits of 1.5 * 2^23
-
-  // ---- stage the window: knots, per-layer boresight cells, per-layer constants, spline system, detector constants ----
-  for (int k = tid; k < Wn; k += F32_THREADS) {
-    const double* b = P.bore_atm + 4 * (size_t)(wa + k);
-    Knot<float> o;
-    o.ce = (float)b[0];
-    o.se = (float)b[1];
-    o.ca = (float)b[2];
-    o.sa = (float)b[3];
-    knots[k] = o;
-  }
-  for (int e = tid; e < n_layers * Wn; e += F32_THREADS) {
-    const int l = e / Wn, k = e % Wn;
-    const double* b = P.layers[l].base + 2 * (size_t)(wa + k);
-    const double cx = b[0], cy = b[1];
-    const double flx = fmin(fmax(floor(cx), -1.0e9), 1.0e9), fly = fmin(fmax(floor(cy), -1.0e9), 1.0e9);
-    LayerKnot<float> o;
-    o.ix = (int)flx;
-    o.iy = (int)fly;
-    o.fx = (float)(cx - flx);
-    o.fy = (float)(cy - fly);
-    lk[l * F32_W + k] = o;
-  }
-  if (tid < n_layers) {
-    const LayerDev& L = P.layers[tid];
-    LayerF o;
-    o.D0 = (float)L.D[0];
-    o.D1 = (float)L.D[1];
-    o.D2 = (float)L.D[2];
-    o.D3 = (float)L.D[3];
-    o.rms = (float)L.pwv_rms;
-    o.ne1 = L.n_ext - 1;
-    o.nc1 = L.n_cs - 1;
-    o.n_cs = L.n_cs;
-    o.data = reinterpret_cast<const float*>(L.data);
-    o.pad[0] = o.pad[1] = 0;
-    ls[tid] = o;
-  }
-  if (tid < F32_DT) {
-    const int dd = tid;
-    float u = 0.f, w = 1.f, g = 0.f;
-    int band = 0;
-    long long row = 0;
-    if (dd < nd) {
-      const int64_t d = order[dbase + dd];  // absolute detector index of this slot
-      row = (d - det0) * P.n_t;
-      u = (float)P.det_full[2 * d];
-      w = (float)P.det_full[2 * d + 1];
-      g = apply_gain ? (float)P.gain[d] : 1.f;
-      band = P.band_index[d];
-    }
-    dc_gain[dd] = g;
-    dc_band[dd] = band;
-    dc_row[dd] = row;
-    float* uw = reinterpret_cast<float*>(dc_uw);
-    uw[(dd >> 1) * 4 + (dd & 1)] = u;
-    uw[(dd >> 1) * 4 + 2 + (dd & 1)] = w;
-    reinterpret_cast<int*>(dc_tab)[dd] = band * P.calq_n - MAGIC_BITS;
-  }
-  for (int k = tid; k < Wn; k += F32_THREADS) {
-    const double* sp = P.spl + 5 * (size_t)(wa + k);
-    splq[k] = make_float4((float)sp[0], (float)sp[2], (float)sp[3], (float)sp[4]);
-    h26[k] = (float)sp[1];
-  }
-  __syncthreads();
-
-  // ---- phase 1: loading [pW] at the window's knots ----
-  // Each thread works on F32_G knots at once: F32_G independent gather chains per layer keep 4 F32_G loads in flight
-  // (the layers live in L2; a dependent chain per knot leaves the SM waiting on that latency), and the per-layer
-  // constants are fetched once per group.
+// Phase 1 of the fused kernel: loading [pW] at the window's knots, for a tile whose detectors come in groups of M
+// co-located ones (dichroic pixels, both polarisations: same offsets, hence the same line of sight through every layer).
+// Each thread works on F32_G knots at once: F32_G independent gather chains per layer keep 4 F32_G loads in flight (the
+// layers live in L2; a dependent chain per knot leaves the SM waiting on that latency), and the per-layer constants are
+// fetched once per group.
+template <int M>
+__device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* __restrict__ order, int64_t dbase, int nd, int wa,
+                                           int Wn, int n_layers, const Knot<float>* knots, const LayerKnot<float>* lk,
+                                           const LayerF* ls, float* ymf, const float* dc_gain, const int* dc_band,
+                                           const float* dc_mu, int lane, int warp) {
   {
-    const int64_t d = order[dbase + min(lane, nd - 1)];  // idle lanes of a partial tile shadow the last detector
+    // M detectors share every line of sight: lanes [0, 32 / M) of a warp are the tile's positions, the other lanes take
+    // further knots (M "virtual warps" per warp), and each lane finishes M detectors (band tables, Mueller, gain)
+    constexpr int PL = 32 / M;
+    const int slot0 = (lane % PL) * M, sub = lane / PL;
+    const int64_t d = order[dbase + min(slot0, nd - 1)];  // idle lanes of a partial tile shadow the last detector
     const double* da = P.det_atm + 4 * d;
     const float u = (float)da[0], Y = (float)da[1], wm1 = (float)da[2];
-    const int band = P.band_index[d];
-    const float mu = (float)P.mueller00[d];
     const float pwv0 = (float)P.pwv0;
-    const float gain_d = dc_gain[lane];
     int ip = 0, ie = 0;
-    float* yrow = ymf + (lane >> 1) * 4 + (lane & 1);
-    constexpr int NW = F32_THREADS / 32;
-    for (int kb = warp; kb < Wn; kb += NW * F32_G) {
+    constexpr int NW = (F32_THREADS / 32) * M;
+    for (int kb = warp * M + sub; kb < Wn; kb += NW * F32_G) {
       float dppx[F32_G], dppy[F32_G], sinel[F32_G], acc[F32_G];
       int kk[F32_G];
       bool bad = false;
@@ -276,10 +186,127 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
           if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, wa + kk[q]);
           if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
         }
-        const float y = loading_pW<float>(P, band, mu, pwv0 + acc[q], sinel[q], ip, ie);
-        if (kb + q * NW < Wn) yrow[kk[q] * (F32_NP * 4)] = y * gain_d;  // the spline is linear in the data: gain goes in here
+#pragma unroll
+        for (int j = 0; j < M; j++) {
+          const int sl = slot0 + j;
+          const float y = loading_pW<float>(P, dc_band[sl], dc_mu[sl], pwv0 + acc[q], sinel[q], ip, ie);
+          // the spline is linear in the data: the detector gain goes in here
+          if (kb + q * NW < Wn) ymf[(kk[q] * F32_NP + (sl >> 1)) * 4 + (sl & 1)] = y * dc_gain[sl];
+        }
       }
     }
+  }
+}
+
+__global__ void __launch_bounds__(F32_THREADS, F32_MINB)
+    synth_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order,
+                     const uint8_t* __restrict__ tile_m, int64_t det0, int64_t n_det,
+                     float* __restrict__ out, int units, int apply_gain) {
+  extern __shared__ __align__(16) unsigned char dyn[];
+  float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_d0, y_d1, m_d0, m_d1}
+  float* ymf = reinterpret_cast<float*>(dyn);
+  float4* splq = ym4 + F32_W * F32_NP;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
+  float* h26 = reinterpret_cast<float*>(splq + F32_W);               // [W] h_k^2 / 6
+  Knot<float>* knots = reinterpret_cast<Knot<float>*>(reinterpret_cast<float*>(splq) + F32_SPLN);
+  LayerKnot<float>* lk = reinterpret_cast<LayerKnot<float>*>(knots + F32_W);  // [n_layers][W]
+  __shared__ __align__(16) LayerF ls[MATM_MAX_LAYERS];
+  __shared__ float4 dc_uw[F32_NP];  // {u_d0, u_d1, w_d0, w_d1} of the rolled offsets
+  __shared__ int2 dc_tab[F32_NP];   // calibration-table base of each detector's band, minus the rounding magic
+  __shared__ float dc_gain[F32_DT];
+  __shared__ int dc_band[F32_DT];
+  __shared__ float dc_mu[F32_DT];
+  __shared__ __align__(16) long long dc_row[F32_DT];  // element offset of each detector's output row
+
+  const int n = P.n_t_atm;
+  const int n_int = n - 1;
+  const int n_layers = P.n_layers;
+  const int n_ttiles = (n_int + F32_KT - 1) / F32_KT;
+  const int64_t dtile = blockIdx.x / n_ttiles;
+  const int ttile = blockIdx.x % n_ttiles;
+  const int k0 = ttile * F32_KT, k1 = min(k0 + F32_KT, n_int);
+  const int wa = max(0, k0 - F32_HALO), wb = min(n - 1, k1 + F32_HALO);
+  const int Wn = wb - wa + 1;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t dbase = dtile * F32_DT;
+  const int nd = (int)min((int64_t)F32_DT, n_det - dbase);
+  constexpr int MAGIC_BITS = 0x4B400000;  // bits of 1.5 * 2^23
+
+  // ---- stage the window: knots, per-layer boresight cells, per-layer constants, spline system, detector constants ----
+  for (int k = tid; k < Wn; k += F32_THREADS) {
+    const double* b = P.bore_atm + 4 * (size_t)(wa + k);
+    Knot<float> o;
+    o.ce = (float)b[0];
+    o.se = (float)b[1];
+    o.ca = (float)b[2];
+    o.sa = (float)b[3];
+    knots[k] = o;
+  }
+  for (int e = tid; e < n_layers * Wn; e += F32_THREADS) {
+    const int l = e / Wn, k = e % Wn;
+    const double* b = P.layers[l].base + 2 * (size_t)(wa + k);
+    const double cx = b[0], cy = b[1];
+    const double flx = fmin(fmax(floor(cx), -1.0e9), 1.0e9), fly = fmin(fmax(floor(cy), -1.0e9), 1.0e9);
+    LayerKnot<float> o;
+    o.ix = (int)flx;
+    o.iy = (int)fly;
+    o.fx = (float)(cx - flx);
+    o.fy = (float)(cy - fly);
+    lk[l * F32_W + k] = o;
+  }
+  if (tid < n_layers) {
+    const LayerDev& L = P.layers[tid];
+    LayerF o;
+    o.D0 = (float)L.D[0];
+    o.D1 = (float)L.D[1];
+    o.D2 = (float)L.D[2];
+    o.D3 = (float)L.D[3];
+    o.rms = (float)L.pwv_rms;
+    o.ne1 = L.n_ext - 1;
+    o.nc1 = L.n_cs - 1;
+    o.n_cs = L.n_cs;
+    o.data = reinterpret_cast<const float*>(L.data);
+    o.pad[0] = o.pad[1] = 0;
+    ls[tid] = o;
+  }
+  if (tid < F32_DT) {
+    const int dd = tid;
+    float u = 0.f, w = 1.f, g = 0.f, mu = 0.f;
+    int band = 0;
+    long long row = 0;
+    if (dd < nd) {
+      const int64_t d = order[dbase + dd];  // absolute detector index of this slot
+      row = (d - det0) * P.n_t;
+      u = (float)P.det_full[2 * d];
+      w = (float)P.det_full[2 * d + 1];
+      g = apply_gain ? (float)P.gain[d] : 1.f;
+      band = P.band_index[d];
+      mu = (float)P.mueller00[d];
+    }
+    dc_mu[dd] = mu;
+    dc_gain[dd] = g;
+    dc_band[dd] = band;
+    dc_row[dd] = row;
+    float* uw = reinterpret_cast<float*>(dc_uw);
+    uw[(dd >> 1) * 4 + (dd & 1)] = u;
+    uw[(dd >> 1) * 4 + 2 + (dd & 1)] = w;
+    reinterpret_cast<int*>(dc_tab)[dd] = band * P.calq_n - MAGIC_BITS;
+  }
+  for (int k = tid; k < Wn; k += F32_THREADS) {
+    const double* sp = P.spl + 5 * (size_t)(wa + k);
+    splq[k] = make_float4((float)sp[0], (float)sp[2], (float)sp[3], (float)sp[4]);
+    h26[k] = (float)sp[1];
+  }
+  __syncthreads();
+
+  // ---- phase 1: loading [pW] at the window's knots (phase1_f32) ----
+  {
+    const int tm = nd == F32_DT ? tile_m[dtile] : 1;
+    if (tm == 4)
+      phase1_f32<4>(P, order, dbase, nd, wa, Wn, n_layers, knots, lk, ls, ymf, dc_gain, dc_band, dc_mu, lane, warp);
+    else if (tm == 2)
+      phase1_f32<2>(P, order, dbase, nd, wa, Wn, n_layers, knots, lk, ls, ymf, dc_gain, dc_band, dc_mu, lane, warp);
+    else
+      phase1_f32<1>(P, order, dbase, nd, wa, Wn, n_layers, knots, lk, ls, ymf, dc_gain, dc_band, dc_mu, lane, warp);
   }
   __syncthreads();
 
