@@ -52,10 +52,17 @@ def c3_multiband(n_det=3000, duration=600.0, sample_rate=50.0, pwv=1.0):
 
 def c4_atlast(n_det=100_000, duration=3600.0, sample_rate=50.0, n_groups=1):
     """AtLAST-scale: ``n_det`` detectors hex-packed in a 2 deg field, 50 m primary, bands 93 / 150 GHz, 1-hour raster.
-    ``n_groups`` > 1 tiles that focal plane (weak-scaling benchmark: one group of ``n_det`` detectors per GPU)."""
+    ``n_groups`` > 1 packs ``n_groups`` such sub-arrays into the field (weak-scaling benchmark: one sub-array of ``n_det``
+    detectors per GPU); detectors are emitted sub-array by sub-array, band-sorted inside each, so that a contiguous
+    detector shard holds every band of its own pixels."""
     bands = [I.Band("f093", center=93e9, width=30e9, efficiency=0.5, gain_error=5e-2),
              I.Band("f150", center=150e9, width=40e9, efficiency=0.5, gain_error=5e-2)]
     inst = I.make_instrument(n_det * n_groups // 2, [bands], 2.0, 50.0, name="AtLAST-like")
+    if n_groups > 1:
+        n_pos, per = n_det * n_groups // 2, n_det // 2
+        perm = np.concatenate([np.concatenate([b * n_pos + np.arange(g * per, (g + 1) * per) for b in range(len(bands))])
+                               for g in range(n_groups)])
+        inst = I.Instrument(inst.dets._subset(perm), name=inst.name)
     plan = I.Plan.generate(duration=duration, sample_rate=sample_rate, scan_center=(120.0, 50.0), scan_pattern="raster",
                            scan_options=dict(radius_deg=1.0, speed_deg=0.5, n_rows=21))
     return _pack("C4 AtLAST 100k raster", inst, plan, I.Site("chajnantor", 5060.0), pwv=1.0, T0=270.0)

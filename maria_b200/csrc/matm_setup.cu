@@ -608,6 +608,10 @@ extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int
     P.Hs_R = base + esz * ((size_t)npwv + 2 * nel + (size_t)n_bands * npwv * nel + (size_t)n_bands * (nel - 1));
   }
   P.table_ok = (ok ? 1 : 0) | (okc ? 2 : 0);
+  P.pwv_lo_f = (float)side_pwv_host[0];
+  P.pwv_hi_f = (float)side_pwv_host[npwv - 1];
+  P.el_lo_f = (float)side_el_host[0];
+  P.el_hi_f = (float)side_el_host[nel - 1];
   if (h->dtype == MATM_F32) {
     std::vector<double> H1h((size_t)n_bands * nel);
     MATM_CUDA(h, cudaMemcpy(H1h.data(), h->H1, H1h.size() * sizeof(double), cudaMemcpyDeviceToHost));

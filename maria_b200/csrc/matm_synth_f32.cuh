@@ -89,6 +89,55 @@ __device__ __noinline__ float cal_factor_special(const SynthParams& P, int idx, 
   return 1.0f / den;
 }
 
+// a11 + a12 for this kernel, in two parts.  The cell of the folded (pwv, el) grid and the two weights depend on the line of
+// sight only, so co-located detectors share them; the band's table is then one bilinear blend per detector.  The grid
+// values met during the search are the cell's corners (no second fetch), the table ends come from the parameter block.
+// Same interval as find_interval (np.searchsorted - 1, clipped), same NaN / flag behaviour as loading_pW.
+__device__ __forceinline__ bool emission_cell_f32(const SynthParams& P, float zpwv, float sin_el, int& ip, int& ie, float& wp,
+                                                  float& we) {
+  const float* __restrict__ gp = reinterpret_cast<const float*>(P.pwv_R);
+  const float* __restrict__ ge = reinterpret_cast<const float*>(P.el_R);
+  const float el = fast_asin(sin_el);  // <= pi/2 by construction, so the reference's clip(max=pi/2) is the identity
+  float p0 = __ldg(gp + ip), p1 = __ldg(gp + ip + 1);
+  while (ip > 0 && !(p0 < zpwv)) {
+    ip--;
+    p1 = p0;
+    p0 = __ldg(gp + ip);
+  }
+  while (ip < P.npwv - 2 && p1 < zpwv) {
+    ip++;
+    p0 = p1;
+    p1 = __ldg(gp + ip + 1);
+  }
+  float e0 = __ldg(ge + ie), e1 = __ldg(ge + ie + 1);
+  while (ie > 0 && !(e0 < el)) {
+    ie--;
+    e1 = e0;
+    e0 = __ldg(ge + ie);
+  }
+  while (ie < P.nel - 2 && e1 < el) {
+    ie++;
+    e0 = e1;
+    e1 = __ldg(ge + ie + 1);
+  }
+  const bool ok = !(zpwv < P.pwv_lo_f || zpwv > P.pwv_hi_f || el < P.el_lo_f || el > P.el_hi_f) && (zpwv == zpwv) &&
+                  (P.table_ok & 1);
+  if (!ok) {
+    if (zpwv == zpwv) atomicOr(&P.flags[0], 2);  // NaN from an out-of-grid layer is already flagged
+    return false;
+  }
+  wp = (zpwv - p0) * fast_rcp(p1 - p0);
+  we = (el - e0) * fast_rcp(e1 - e0);
+  return true;
+}
+
+__device__ __forceinline__ float emission_blend_f32(const SynthParams& P, int band, int ip, int ie, float wp, float we) {
+  const float* __restrict__ g = reinterpret_cast<const float*>(P.G2_R) + ((band * P.npwv + ip) * P.nel + ie);
+  const float g00 = __ldg(g), g01 = __ldg(g + 1), g10 = __ldg(g + P.nel), g11 = __ldg(g + P.nel + 1);
+  const float a = fmaf(we, g01 - g00, g00), b = fmaf(we, g11 - g10, g10);
+  return fmaf(wp, b - a, a);
+}
+
 // Phase 1 of the fused kernel: loading [pW] at the window's knots, for a tile whose detectors come in groups of M
 // co-located ones (dichroic pixels, both polarisations: same offsets, hence the same line of sight through every layer).
 // Each thread works on F32_G knots at once: F32_G independent gather chains per layer keep 4 F32_G loads in flight (the
@@ -186,12 +235,14 @@ __device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* 
           if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, wa + kk[q]);
           if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
         }
+        float wp, we;
+        const bool ok = emission_cell_f32(P, pwv0 + acc[q], sinel[q], ip, ie, wp, we);
 #pragma unroll
         for (int j = 0; j < M; j++) {
           const int sl = slot0 + j;
-          const float y = loading_pW<float>(P, dc_band[sl], dc_mu[sl], pwv0 + acc[q], sinel[q], ip, ie);
-          // the spline is linear in the data: the detector gain goes in here
-          if (kb + q * NW < Wn) ymf[(kk[q] * F32_NP + (sl >> 1)) * 4 + (sl & 1)] = y * dc_gain[sl];
+          // times Mueller [0,0]; the spline being linear in the data, the detector gain goes in here too
+          const float y = ok ? emission_blend_f32(P, dc_band[sl], ip, ie, wp, we) * dc_mu[sl] * dc_gain[sl] : r_nan<float>();
+          if (kb + q * NW < Wn) ymf[(kk[q] * F32_NP + (sl >> 1)) * 4 + (sl & 1)] = y;
         }
       }
     }
