@@ -159,6 +159,22 @@ def test_c4_properties_on_device(cuda, c4):
     atm.check_flags()
 
 
+def test_colocated_detectors_share_the_line_of_sight_bit_exactly(cuda):
+    """Weak-scaling layout (sub-array by sub-array, both bands of a pixel in the same shard): a shard whose detectors pair
+    up runs the shared-line-of-sight phase 1; dropping its first detector shifts every pair apart (one position per
+    detector again).  Both give the same bits, and both match the fp64 oracle."""
+    cfg = configs.c4_atlast(n_det=512, duration=120.0, sample_rate=50.0, n_groups=2)
+    dets = cfg["instrument"].dets
+    assert np.array_equal(dets.offsets[:256], dets.offsets[256:512]) and dets.band_name[0] != dets.band_name[256]
+    sim = _device(cfg, np.float32, 29, geometry="exact")
+    full = sim.run(units="K_RJ")[0].data["atmosphere"]
+    _check32(full, _oracle(cfg, seed=29)["tod_K_RJ"])
+    obs = sim.obs_list[0]
+    shard = sim._compute_atmospheric_loading(obs, 512, 512, units="K_RJ", apply_gain=True).cpu().numpy()    # rank 1 of 2: paired
+    unpaired = sim._compute_atmospheric_loading(obs, 513, 511, units="K_RJ", apply_gain=True).cpu().numpy()
+    assert np.array_equal(shard, full[512:]) and np.array_equal(unpaired, full[513:])
+
+
 def test_c5_six_hour_scan_runs_and_matches_oracle_subset(cuda):
     """C5's time axis (6 h at 50 Hz = 1.08 M samples per detector, ~48 k knots, layers six times longer than C4's) on a
     thinned focal plane: the float32 path against the oracle fed with the device's layers, and no line of sight leaves a
