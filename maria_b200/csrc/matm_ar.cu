@@ -344,11 +344,255 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// The chain, v4: the same register-resident layout as v3, with the cluster barrier replaced by data-carrying signals.
+// Every value travels with its own completion: the owner of (row i, column c) sends it with st.async into the gather
+// vectors of steps i-1, i-2, i-3 of every CTA, each store completing bytes on an mbarrier of the DESTINATION CTA.  A
+// gather vector has two mbarriers: EARLY (stencil offsets 2, 3 and the far samples: everything known one step ahead)
+// and LATE (offset 1: the row just produced).  A step therefore waits only for the bytes it needs, there is no fence
+// and no barrier round trip on the critical path, and the part of the dot product that uses the EARLY entries of the
+// NEXT step (more than half of a row of A) is computed while the LATE entries are still in flight.
+// Buffer reuse needs no extra synchronisation: a value of step i can only be sent after the LATE barrier of step i
+// completed, i.e. after every publishing warp of every CTA has finished reading the vectors of steps > i.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t a, int cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void st_async_f64(uint32_t remote_addr, double v, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];" ::"r"(remote_addr), "d"(v),
+               "r"(remote_bar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arm(uint32_t bar, uint32_t bytes) {
+  if (bytes == 0)
+    mbar_arrive(bar);
+  else
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// wait for the phase of the given parity; data written by st.async of other CTAs is visible afterwards.  A wait that
+// never ends is a bug in the byte accounting: trap instead of hanging the device.
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  int spins = 0;
+  while (!done) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"  // transaction barrier: the bytes it counted are visible
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!done && ++spins > (1 << 22)) __trap();
+  }
+}
+
+template <int L, int MP>
+__global__ void __launch_bounds__(AR_THREADS, 1)
+    ar_chain_v4_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
+                       double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl) {
+  constexpr int RPW = 32 / L;  // rows per warp
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int gs = L * MP;                                     // padded length of one gather vector
+  double* G = reinterpret_cast<double*>(smem_raw);           // [4][gs]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(G + 4 * (size_t)gs);  // [4] LATE, [4] EARLY
+  int* cnt = reinterpret_cast<int*>(bars + 8);               // [4]: near samples of offset 1, 2, 3
+  int* pos = cnt + 4;                                        // [3][n_cs]: position of column c among the samples of offset 1, 2, 3
+  const int n_far = n_sample - n_near;
+  int cta = 0;
+  if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
+  const int rpc = (n_cs + cl - 1) / cl;
+  const int row0 = cta * rpc;
+  const int rows = max(0, min(n_cs, row0 + rpc) - row0);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rr = lane / L, sub = lane % L;
+  const int r = warp * RPW + rr;  // row within this CTA
+  const bool has_row = r < rows;
+  const int i_top = 2 * n_ext - 1;
+  const uint32_t G_s = smem_u32(G), bars_s = smem_u32(bars);
+
+  // ---- set-up: A into registers, G zeroed, inverse stencil maps, sample counts per offset ----
+  double a[MP];
+#pragma unroll
+  for (int m = 0; m < MP; m++) {
+    const int s = sub + L * m;
+    a[m] = (has_row && s < n_sample) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
+  }
+  for (int e = tid; e < 4 * gs; e += AR_THREADS) G[e] = 0.0;
+  for (int e = tid; e < 3 * n_cs; e += AR_THREADS) pos[e] = -1;
+  if (tid < 4) cnt[tid] = 0;
+  if (tid == 0) {
+    for (int b = 0; b < 8; b++) mbar_init(bars + b, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  for (int s = tid; s < n_near; s += AR_THREADS) {
+    pos[esi[s] * n_cs + csi[s]] = s;  // offset = esi + 1 in 1..3
+    atomicAdd(&cnt[esi[s]], 1);
+  }
+  int foff[2];
+#pragma unroll
+  for (int q = 0; q < 2; q++) {
+    const int f = tid + q * AR_THREADS;
+    foff[q] = f < n_far ? (esi[n_near + f] + 1) * n_cs + csi[n_near + f] : -1;
+  }
+  __syncthreads();
+  const int n1 = cnt[0], n2 = cnt[1], n3 = cnt[2];
+  // registers [0, mcrit) hold every offset-1 sample (the samples are sorted by offset): the part of the dot product that
+  // has to wait for the row just produced; the rest is computed one step ahead
+  const int mcrit = min(MP, 4 * ((n1 + 4 * L - 1) / (4 * L)));
+  int p1 = -1, p2 = -1, p3 = -1;
+  if (has_row && sub == 0) {
+    p1 = pos[row0 + r];
+    p2 = pos[n_cs + row0 + r];
+    p3 = pos[2 * n_cs + row0 + r];
+  }
+  // ---- prologue: the initial-noise rows i_top+1 .. i_top+3 feed steps i_top, i_top-1, i_top-2 ----
+  for (int e = tid; e < 3 * n_near; e += AR_THREADS) {
+    const int k = e / n_near, s = e % n_near;  // step i_top - k, near sample s
+    const int off = esi[s] + 1;
+    if (off > k && i_top - k >= 0)
+      G[((i_top - k) & 3) * gs + s] = buffer[(size_t)(i_top - k + off) * n_cs + csi[s]];
+  }
+#pragma unroll
+  for (int q = 0; q < 2; q++)
+    if (foff[q] >= 0) {
+      const int f = n_near + tid + q * AR_THREADS;
+      G[(i_top & 3) * gs + f] = buffer[(size_t)i_top * n_cs + foff[q]];
+      if (i_top >= 1) G[((i_top - 1) & 3) * gs + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
+    }
+  // Register pipelines, two sets each, used alternately by even / odd steps (the loop is unrolled by two):
+  //   far_s[i & 1]: issued at step i + 4 for step i - 2, sent into G at step i, then re-issued for step i - 4
+  //   bz_s[i & 1] : issued at step i + 2 for step i, consumed when step i publishes, then re-issued for step i - 2
+  double far_s[2][2], bz_s[2];
+  far_s[0][0] = far_s[0][1] = far_s[1][0] = far_s[1][1] = 0.0;
+  bz_s[0] = bz_s[1] = 0.0;
+  if (has_row) {  // i_top is odd: set 1 serves step i_top, set 0 step i_top - 1
+    bz_s[1] = buffer[(size_t)i_top * n_cs + row0 + r];
+    bz_s[0] = buffer[(size_t)(i_top - 1) * n_cs + row0 + r];
+  }
+#pragma unroll
+  for (int q = 0; q < 2; q++)
+    if (foff[q] >= 0) {
+      if (i_top >= 2) far_s[1][q] = buffer[(size_t)(i_top - 2) * n_cs + foff[q]];
+      if (i_top >= 3) far_s[0][q] = buffer[(size_t)(i_top - 3) * n_cs + foff[q]];
+    }
+  // bytes each barrier expects for step j = i_top - d: what the loop (not the prologue) delivers
+  const uint32_t late_full = 8u * n1, early_full = 8u * (n2 + n3 + n_far);
+  if (tid == 0) {
+    for (int d = 0; d < 4 && d <= i_top; d++) {
+      const int b = (i_top - d) & 3;
+      mbar_arm(bars_s + 8 * b, d >= 1 ? late_full : 0u);
+      mbar_arm(bars_s + 8 * (4 + b), (d >= 2 ? 8u * (n2 + n_far) : 0u) + (d >= 3 ? 8u * n3 : 0u));
+    }
+    // nobody waits for the EARLY barrier of step i_top (its part is computed right below): arm its next use here
+    if (i_top >= 4) mbar_arm(bars_s + 8 * (4 + (i_top & 3)), early_full);
+  }
+  __syncthreads();
+  cluster_barrier();
+
+  // the EARLY part of the dot product of step j: registers [mcrit, MP)
+  auto early_part = [&](const int j) -> double {
+    const double* g = G + (j & 3) * gs + sub;
+    double e0 = 0.0, e1 = 0.0, e2 = 0.0, e3 = 0.0;
+#pragma unroll
+    for (int m = 0; m < MP; m += 4)
+      if (m >= mcrit) {
+        e0 = fma(a[m], g[L * m], e0);
+        if (m + 1 < MP) e1 = fma(a[m + 1], g[L * (m + 1)], e1);
+        if (m + 2 < MP) e2 = fma(a[m + 2], g[L * (m + 2)], e2);
+        if (m + 3 < MP) e3 = fma(a[m + 3], g[L * (m + 3)], e3);
+      }
+    return (e0 + e1) + (e2 + e3);
+  };
+  // warps with neither a row nor a far sample only wait for the end
+  const bool active = (warp * RPW < rows) || (warp * 32 < n_far);
+  double pre = 0.0;
+  if (active) {
+    pre = early_part(i_top);
+
+    auto step = [&](const int i, double(&fs)[2], double& bz) {
+      const uint32_t par = ((i_top - i) >> 2) & 1;
+      // (1) the row just produced has landed in G[i]
+      mbar_wait_cluster(bars_s + 8 * (i & 3), par);
+      if (tid == 0 && i >= 4) mbar_arm(bars_s + 8 * (i & 3), late_full);
+      // (2) the LATE part of the dot product
+      const double* g = G + (i & 3) * gs + sub;
+      double acc0 = pre, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+#pragma unroll
+      for (int m = 0; m < MP; m += 4)
+        if (m < mcrit) {
+          acc0 = fma(a[m], g[L * m], acc0);
+          if (m + 1 < MP) acc1 = fma(a[m + 1], g[L * (m + 1)], acc1);
+          if (m + 2 < MP) acc2 = fma(a[m + 2], g[L * (m + 2)], acc2);
+          if (m + 3 < MP) acc3 = fma(a[m + 3], g[L * (m + 3)], acc3);
+        }
+      double acc = (acc0 + acc1) + (acc2 + acc3);
+#pragma unroll
+      for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      // (3) publish row r of step i into the gather vectors of steps i-1, i-2, i-3 of every CTA, and to global memory
+      if (has_row && sub == 0) {
+        const double v = bz + acc;
+        const uint32_t d1 = G_s + 8u * (((i - 1) & 3) * gs + p1), b1 = bars_s + 8u * ((i - 1) & 3);
+        const uint32_t d2 = G_s + 8u * (((i - 2) & 3) * gs + p2), b2 = bars_s + 8u * (4 + ((i - 2) & 3));
+        const uint32_t d3 = G_s + 8u * (((i - 3) & 3) * gs + p3), b3 = bars_s + 8u * (4 + ((i - 3) & 3));
+        buffer[(size_t)i * n_cs + row0 + r] = v;  // read again (far samples) no sooner than three steps from now
+        for (int c = 0; c < cl; c++) {
+          if (p1 >= 0 && i >= 1) st_async_f64(mapa_u32(d1, c), v, mapa_u32(b1, c));
+          if (p2 >= 0 && i >= 2) st_async_f64(mapa_u32(d2, c), v, mapa_u32(b2, c));
+          if (p3 >= 0 && i >= 3) st_async_f64(mapa_u32(d3, c), v, mapa_u32(b3, c));
+        }
+      }
+      // (4) off the critical path: send the far values of step i - 2 (in flight since step i + 4), re-issue the set for
+      //     step i - 4 (rows >= i + 1, complete: their LATE barrier was passed above), re-issue B z for step i - 2
+      if (i >= 2) {
+        const uint32_t be = mapa_u32(bars_s + 8u * (4 + ((i - 2) & 3)), cta);
+#pragma unroll
+        for (int q = 0; q < 2; q++)
+          if (foff[q] >= 0)
+            st_async_f64(mapa_u32(G_s + 8u * (((i - 2) & 3) * gs + n_near + tid + q * AR_THREADS), cta), fs[q], be);
+      }
+      if (i >= 4) {
+#pragma unroll
+        for (int q = 0; q < 2; q++)
+          if (foff[q] >= 0) fs[q] = __ldcg(buffer + (size_t)(i - 4) * n_cs + foff[q]);
+      }
+      if (i >= 2 && has_row) bz = __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r);
+      // (5) the EARLY part of step i - 1, while the row of step i is on its way
+      if (i >= 1) {
+        const uint32_t pe = ((i_top - (i - 1)) >> 2) & 1;
+        mbar_wait_cluster(bars_s + 8 * (4 + ((i - 1) & 3)), pe);
+        if (tid == 0 && i - 1 >= 4) mbar_arm(bars_s + 8 * (4 + ((i - 1) & 3)), early_full);
+        pre = early_part(i - 1);
+      }
+    };
+
+    for (int i = i_top; i >= 1; i -= 2) {  // i_top = 2 n_ext - 1 is odd
+      step(i, far_s[1], bz_s[1]);
+      step(i - 1, far_s[0], bz_s[0]);
+    }
+  }
+  // no CTA may leave while values are still on their way to it
+  cluster_barrier();
+}
+
 template <int L, int MP>
 static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
                            int n_cs, int n_sample, int n_near, int cl, cudaStream_t stream) {
-  const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16;
-  MATM_CUDA(h, cudaFuncSetAttribute(ar_chain_v3_kernel<L, MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static int use_v3 = -1;  // MATM_AR_V3=1: the barrier-per-step kernel (kept for comparison)
+  if (use_v3 < 0) {
+    const char* e = getenv("MATM_AR_V3");
+    use_v3 = (e && atoi(e)) ? 1 : 0;
+  }
+  const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16;
+  auto kernel = use_v3 ? ar_chain_v3_kernel<L, MP> : ar_chain_v4_kernel<L, MP>;
+  MATM_CUDA(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cl, 1, 1);
   cfg.blockDim = dim3(AR_THREADS, 1, 1);
@@ -361,7 +605,7 @@ static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, cons
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, ar_chain_v3_kernel<L, MP>, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl));
+  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, kernel, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl));
   h->launches++;
   return MATM_OK;
 }
