@@ -175,6 +175,40 @@ def test_colocated_detectors_share_the_line_of_sight_bit_exactly(cuda):
     assert np.array_equal(shard, full[512:]) and np.array_equal(unpaired, full[513:])
 
 
+def test_pipelined_realisations_equal_sequential_ones(cuda):
+    """bench.py and Simulation.run keep up to ``pipeline_depth`` realisations' AR chains in flight underneath the synthesis
+    of an earlier one (slots of process buffers, two sets of layer buffers, per-slot streams).  Every realisation must
+    come out bit-identical to generating and synthesising it on its own."""
+    cfg = configs.c4_atlast(n_det=256, duration=240.0, sample_rate=50.0)
+    seeds = [11, 12, 13, 14, 15]
+
+    def make(depth):
+        sim = _device(cfg, np.float32, 31, noise="philox", seed=seeds[0], geometry="fast", pipeline_depth=depth)
+        return sim, sim.obs_list[0].atmosphere
+
+    sim, atm = make(1)
+    sequential = []
+    for sd in seeds:
+        atm.seed = sd
+        atm.generate()
+        sequential.append(atm.synthesize(units="K_RJ", apply_gain=False).clone())
+    assert not cuda.equal(sequential[0], sequential[1])
+    for depth in (2, 3):
+        sim, atm = make(depth)
+        for r in range(depth):
+            atm.seed = seeds[r]
+            atm.generate_async()
+        for i, sd in enumerate(seeds):
+            atm.finish_generate()
+            if i + depth < len(seeds):
+                atm.seed = seeds[i + depth]
+                atm.generate_async()
+            out = atm.synthesize(units="K_RJ", apply_gain=False)
+            assert cuda.equal(out, sequential[i]), (depth, i)
+        atm.join_streams()
+        atm.check_flags()
+
+
 def test_c5_six_hour_scan_runs_and_matches_oracle_subset(cuda):
     """C5's time axis (6 h at 50 Hz = 1.08 M samples per detector, ~48 k knots, layers six times longer than C4's) on a
     thinned focal plane: the float32 path against the oracle fed with the device's layers, and no line of sight leaves a
