@@ -66,6 +66,7 @@ struct SynthParams {
   const float4* calq_aux;  // 2 float4 per record: {c0, c1 for dt <= dt_k, c0, c1 for dt > dt_k}, {dt_k, 0, 0, 0}
   int calq_n;
   float pwv_lo_f, pwv_hi_f, el_lo_f, el_hi_f;  // ends of the fp32 (pwv, el) grids
+  float det_rmax_f;        // largest angular distance of a detector (rolled offsets) from the boresight [rad]
   int table_ok;            // 0 if T0 / cal_T0 / cal_pwv left the table (results are NaN, as the reference)
   int* flags;              // [0] = status bits, [1] = layer, [2..3] = det (lo, hi), [4..5] = sample (lo, hi)
 };

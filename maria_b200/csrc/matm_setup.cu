@@ -296,6 +296,9 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   }
   h->det_order.clear();
   SynthParams& P = h->P;
+  double rmax = 0.0;
+  for (int64_t i = 0; i < n_det; i++) rmax = fmax(rmax, hypot(offsets_full_host[2 * i], offsets_full_host[2 * i + 1]));
+  P.det_rmax_f = (float)(rmax * (1.0 + 1e-6));
   P.n_det = n_det;
   P.det_atm = h->det_atm;
   P.det_full = h->det_full;

@@ -9,6 +9,7 @@
 //            detector PAIRS: 2 LDS.128 + 4 packed FMAs for the spline, and the calibration factor from the
 //            t = sqrt(1 - sin el) table of matm_setup.cu (no asin, no search, no divide).
 #pragma once
+#include <type_traits>
 #include "matm_synth.cuh"
 
 #define F32_DT 32
@@ -70,6 +71,19 @@ __device__ __forceinline__ float fast_asin(float x) {
   p = fmaf(p, a, 1.5707963050f);
   const float r = fmaf(-fast_sqrt(fmaxf(1.0f - a, 0.0f)), p, 1.5707963268f);
   return copysignf(r, x);
+}
+
+// the same for two arguments in [0, 1] at once, given sq = sqrt(1 - x): pi/2 - sq P7(x), the polynomial in packed f32x2
+__device__ __forceinline__ float2 asin01_f32x2(float2 x, float2 sq) {
+  float2 p = f2(0.0012624911f, 0.0012624911f);  // -P7: the subtraction becomes the last FMA
+  p = __ffma2_rn(p, x, f2(-0.0066700901f, -0.0066700901f));
+  p = __ffma2_rn(p, x, f2(0.0170881256f, 0.0170881256f));
+  p = __ffma2_rn(p, x, f2(-0.0308918810f, -0.0308918810f));
+  p = __ffma2_rn(p, x, f2(0.0501743046f, 0.0501743046f));
+  p = __ffma2_rn(p, x, f2(-0.0889789874f, -0.0889789874f));
+  p = __ffma2_rn(p, x, f2(0.2145988016f, 0.2145988016f));
+  p = __ffma2_rn(p, x, f2(-1.5707963050f, -1.5707963050f));
+  return __ffma2_rn(sq, p, f2(1.5707963268f, 1.5707963268f));
 }
 
 // The calibration factor in a special bin of the table (calq_kind != 0): a bin holding one grid point of the elevation
@@ -267,6 +281,8 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   __shared__ int dc_band[F32_DT];
   __shared__ float dc_mu[F32_DT];
   __shared__ __align__(16) long long dc_row[F32_DT];  // element offset of each detector's output row
+  __shared__ float4 dc_cal[F32_NP];  // {Hc_d0, Hc_d1, Hs_d0, Hs_d1}: the line H(el) of the tile's elevation interval (s_cal_ie >= 0)
+  __shared__ int s_cal_ie;
 
   const int n = P.n_t_atm;
   const int n_int = n - 1;
@@ -342,12 +358,49 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     uw[(dd >> 1) * 4 + 2 + (dd & 1)] = w;
     reinterpret_cast<int*>(dc_tab)[dd] = band * P.calq_n - MAGIC_BITS;
   }
+  if (warp == F32_THREADS / 32 - 1) {
+    // a14 without a table when the whole tile stays inside ONE interval of the elevation grid (the usual case: the grid
+    // steps are degrees wide): sin(el) of any detector at any sample of the window lies within the boresight's range at
+    // the knots, widened by the largest detector offset and by twice the largest knot-to-knot change (motion between knots)
+    float lo = 2.f, hi = -2.f, dmax = 0.f;
+    for (int k = lane; k < Wn; k += 32) {
+      const float c = (float)P.bore_atm[4 * (size_t)(wa + k)];
+      const float cn = (float)P.bore_atm[4 * (size_t)(wa + min(k + 1, Wn - 1))];
+      lo = fminf(lo, c);
+      hi = fmaxf(hi, c);
+      dmax = fmaxf(dmax, fabsf(cn - c));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+      hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+      dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    }
+    if (lane == 0) {
+      const float m = P.det_rmax_f + 2.f * dmax + 1e-6f;
+      lo -= m;
+      hi += m;
+      int ie = -1;
+      if ((P.table_ok & 2) && units == MATM_UNITS_KRJ && lo == lo && hi == hi) {
+        const float* __restrict__ sing = reinterpret_cast<const float*>(P.sinel_R);
+        for (int e = 0; e + 1 < P.nel; e++)
+          if (__ldg(sing + e) < lo && hi <= __ldg(sing + e + 1)) ie = e;
+      }
+      s_cal_ie = ie;
+    }
+  }
   for (int k = tid; k < Wn; k += F32_THREADS) {
     const double* sp = P.spl + 5 * (size_t)(wa + k);
     splq[k] = make_float4((float)sp[0], (float)sp[2], (float)sp[3], (float)sp[4]);
     h26[k] = (float)sp[1];
   }
   __syncthreads();
+  if (tid < F32_DT && s_cal_ie >= 0) {
+    const int ho = dc_band[tid] * (P.nel - 1) + s_cal_ie;
+    float* cal = reinterpret_cast<float*>(dc_cal);
+    cal[(tid >> 1) * 4 + (tid & 1)] = __ldg(reinterpret_cast<const float*>(P.Hc_R) + ho);
+    cal[(tid >> 1) * 4 + 2 + (tid & 1)] = __ldg(reinterpret_cast<const float*>(P.Hs_R) + ho);
+  }
 
   // ---- phase 1: loading [pW] at the window's knots (phase1_f32) ----
   {
@@ -450,94 +503,122 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   const int npairs = nd >> 1;
   const float2* __restrict__ calq = P.calq;
   const float2 scale2 = f2(MATM_CAL_SCALE, MATM_CAL_SCALE), magic2 = f2(12582912.f, 12582912.f);
+  // a14 comes in three flavours, chosen per tile (the choice depends on the time window and on the whole focal plane, not
+  // on the detector shard, so shards stay bit-identical): MODE 0 no calibration (pW); MODE 1 the table in t; MODE 2 the
+  // whole tile lies in one interval of the elevation grid, H(el) = Hc + Hs el with el = asin(sin el) from a polynomial,
+  // no load and no special bins.
   // warps start on multiples of 32 samples: a warp's store is then one 128-byte line per row whenever n_t % 32 == 0
-  for (int64_t jb = (j0 & ~(int64_t)31) + tid; jb < j1; jb += F32_THREADS * F32_S) {
-    float a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
-    const float4* yk[F32_S];
-    int jq[F32_S];
+  auto phase3 = [&](auto mode_tag) {
+    constexpr int MODE = decltype(mode_tag)::value;
+    for (int64_t jb = (j0 & ~(int64_t)31) + tid; jb < j1; jb += F32_THREADS * F32_S) {
+      float a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
+      const float4* yk[F32_S];
+      int jq[F32_S];
 #pragma unroll
-    for (int q = 0; q < F32_S; q++) {
-      // a sample index outside the tile repeats the tile's first / last sample: the same value is stored to the same address by
-      // the thread that owns it, which is harmless and keeps the inner loop free of predicates
-      const int64_t j = max(min(jb + q * F32_THREADS, j1 - 1), j0);
-      const double tj = P.t_full[j];
-      int i = (int)floor((tj - t_atm0) * inv_ts);
-      i = min(max(i, k0), k1 - 1);
-      const int li = i - wa;
-      const float s = (float)(tj - P.t_atm[i]) * (splq[li].x * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
-      const float hh = h26[li], c = 1.f - s;
-      a1[q] = s;
-      a2[q] = hh * (c * c * c - c);
-      a3[q] = hh * (s * s * s - s);
-      se[q] = ce[q] = 0.f;
-      if (krj) {
-        const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
-        ce[q] = (float)bf.x;
-        se[q] = (float)bf.y;
+      for (int q = 0; q < F32_S; q++) {
+        // a sample index outside the tile repeats the tile's first / last sample: the same value is stored to the same address
+        // by the thread that owns it, which is harmless and keeps the inner loop free of predicates
+        const int64_t j = max(min(jb + q * F32_THREADS, j1 - 1), j0);
+        const double tj = P.t_full[j];
+        int i = (int)floor((tj - t_atm0) * inv_ts);
+        i = min(max(i, k0), k1 - 1);
+        const int li = i - wa;
+        const float s = (float)(tj - P.t_atm[i]) * (splq[li].x * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
+        const float hh = h26[li], c = 1.f - s;
+        a1[q] = s;
+        a2[q] = hh * (c * c * c - c);
+        a3[q] = hh * (s * s * s - s);
+        se[q] = ce[q] = 0.f;
+        if constexpr (MODE != 0) {
+          const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
+          ce[q] = (float)bf.x;
+          se[q] = (float)bf.y;
+        }
+        yk[q] = ym4 + li * F32_NP;
+        jq[q] = (int)j;
       }
-      yk[q] = ym4 + li * F32_NP;
-      jq[q] = (int)j;
-    }
 #pragma unroll 2
-    for (int p = 0; p < npairs; p++) {
-      const float4 uw = dc_uw[p];
-      const int2 tb = dc_tab[p];
-      const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
-      float* r0 = out + ro.x;
-      float* r1 = out + ro.y;
-      asm("" : "+l"(r0), "+l"(r1));  // keep the row pointers as they are: each store is then one mad.wide + one st
+      for (int p = 0; p < npairs; p++) {
+        const float4 uw = dc_uw[p];
+        int2 tb = make_int2(0, 0);
+        float4 cal = make_float4(0.f, 0.f, 0.f, 0.f);
+        if constexpr (MODE == 1) tb = dc_tab[p];
+        if constexpr (MODE == 2) cal = dc_cal[p];
+        const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
+        float* r0 = out + ro.x;
+        float* r1 = out + ro.y;
+        asm("" : "+l"(r0), "+l"(r1));  // keep the row pointers as they are: each store is then one mad.wide + one st
 #pragma unroll
-      for (int q = 0; q < F32_S; q++) {
-        const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
-        const float a0 = 1.f - a1[q];
-        float2 v = __fmul2_rn(f2(a0, a0), f2(q0.x, q0.y));
-        v = __ffma2_rn(f2(a1[q], a1[q]), f2(q1.x, q1.y), v);
-        v = __ffma2_rn(f2(a2[q], a2[q]), f2(q0.z, q0.w), v);
-        v = __ffma2_rn(f2(a3[q], a3[q]), f2(q1.z, q1.w), v);
-        if (krj) {
-          const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
-          // |1 - sin el|: sin el can exceed 1 by an ulp; inputs are finite (checked by matm_set_scan / matm_set_detectors)
-          const float2 t = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));
-          const float2 x = __ffma2_rn(t, scale2, magic2);  // round(t * scale) in the low mantissa bits
-          const float2 r = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
-          const float2 dt = __ffma2_rn(t, scale2, f2(-r.x, -r.y));
-          const int i0 = __float_as_int(x.x) + tb.x, i1 = __float_as_int(x.y) + tb.y;
-          const float2 c0 = __ldg(calq + i0), c1 = __ldg(calq + i1);
-          float2 f = f2(fmaf(c0.y, dt.x, c0.x), fmaf(c1.y, dt.y, c1.x));
-          if (!(f.x * f.y == f.x * f.y)) {  // a bin with a grid point of the elevation table, or outside the table
-            if (!(f.x == f.x)) f.x = cal_factor_special(P, i0, dc_band[2 * p], sn.x, dt.x);
-            if (!(f.y == f.y)) f.y = cal_factor_special(P, i1, dc_band[2 * p + 1], sn.y, dt.y);
+        for (int q = 0; q < F32_S; q++) {
+          const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
+          const float a0 = 1.f - a1[q];
+          float2 v = __fmul2_rn(f2(a0, a0), f2(q0.x, q0.y));
+          v = __ffma2_rn(f2(a1[q], a1[q]), f2(q1.x, q1.y), v);
+          v = __ffma2_rn(f2(a2[q], a2[q]), f2(q0.z, q0.w), v);
+          v = __ffma2_rn(f2(a3[q], a3[q]), f2(q1.z, q1.w), v);
+          if constexpr (MODE == 1) {
+            const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
+            // |1 - sin el|: sin el can exceed 1 by an ulp; inputs are finite (checked by matm_set_scan / matm_set_detectors)
+            const float2 t = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));
+            const float2 x = __ffma2_rn(t, scale2, magic2);  // round(t * scale) in the low mantissa bits
+            const float2 r = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
+            const float2 dt = __ffma2_rn(t, scale2, f2(-r.x, -r.y));
+            const int i0 = __float_as_int(x.x) + tb.x, i1 = __float_as_int(x.y) + tb.y;
+            const float2 c0 = __ldg(calq + i0), c1 = __ldg(calq + i1);
+            float2 f = f2(fmaf(c0.y, dt.x, c0.x), fmaf(c1.y, dt.y, c1.x));
+            if (!(f.x * f.y == f.x * f.y)) {  // a bin with a grid point of the elevation table, or outside the table
+              if (!(f.x == f.x)) f.x = cal_factor_special(P, i0, dc_band[2 * p], sn.x, dt.x);
+              if (!(f.y == f.y)) f.y = cal_factor_special(P, i1, dc_band[2 * p + 1], sn.y, dt.y);
+            }
+            v = __fmul2_rn(v, f);
+          } else if constexpr (MODE == 2) {
+            const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
+            const float2 sq = f2(fast_sqrt(fmaxf(1.f - sn.x, 0.f)), fast_sqrt(fmaxf(1.f - sn.y, 0.f)));
+            const float2 el = asin01_f32x2(sn, sq);
+            const float2 den = __ffma2_rn(f2(cal.z, cal.w), el, f2(cal.x, cal.y));
+            v = __fmul2_rn(v, f2(fast_rcp(den.x), fast_rcp(den.y)));
           }
-          v = __fmul2_rn(v, f);
+          st_row(r0, jq[q], v.x);
+          st_row(r1, jq[q], v.y);
         }
-        st_row(r0, jq[q], v.x);
-        st_row(r1, jq[q], v.y);
       }
-    }
-    if (nd & 1) {  // odd tail detector of a partial tile; the same arithmetic as the paired path (bit-identical shards)
-      const int p = npairs;
-      const float uu = dc_uw[p].x, ww = dc_uw[p].z;
-      const int tbx = dc_tab[p].x;
-      float* __restrict__ r0 = out + dc_row[2 * p];
+      if (nd & 1) {  // odd tail detector of a partial tile; the same arithmetic as the paired path (bit-identical shards)
+        const int p = npairs;
+        const float uu = dc_uw[p].x, ww = dc_uw[p].z;
+        const int tbx = dc_tab[p].x;
+        const float hc = dc_cal[p].x, hs = dc_cal[p].z;
+        float* __restrict__ r0 = out + dc_row[2 * p];
 #pragma unroll
-      for (int q = 0; q < F32_S; q++) {
-        const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
-        float v = fmaf(a3[q], q1.z, fmaf(a2[q], q0.z, fmaf(a1[q], q1.x, (1.f - a1[q]) * q0.x)));
-        if (krj) {
-          const float sn = fmaf(uu, se[q], ww * ce[q]);
-          const float t = fast_sqrt(fabsf(1.f - sn));
-          const float x = fmaf(t, MATM_CAL_SCALE, 12582912.f);
-          const float dt = fmaf(t, MATM_CAL_SCALE, -(x - 12582912.f));
-          const int i0 = __float_as_int(x) + tbx;
-          const float2 c0 = __ldg(calq + i0);
-          float f = fmaf(c0.y, dt, c0.x);
-          if (!(f == f)) f = cal_factor_special(P, i0, dc_band[2 * p], sn, dt);
-          v *= f;
+        for (int q = 0; q < F32_S; q++) {
+          const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
+          float v = fmaf(a3[q], q1.z, fmaf(a2[q], q0.z, fmaf(a1[q], q1.x, (1.f - a1[q]) * q0.x)));
+          if constexpr (MODE == 1) {
+            const float sn = fmaf(uu, se[q], ww * ce[q]);
+            const float t = fast_sqrt(fabsf(1.f - sn));
+            const float x = fmaf(t, MATM_CAL_SCALE, 12582912.f);
+            const float dt = fmaf(t, MATM_CAL_SCALE, -(x - 12582912.f));
+            const int i0 = __float_as_int(x) + tbx;
+            const float2 c0 = __ldg(calq + i0);
+            float f = fmaf(c0.y, dt, c0.x);
+            if (!(f == f)) f = cal_factor_special(P, i0, dc_band[2 * p], sn, dt);
+            v *= f;
+          } else if constexpr (MODE == 2) {
+            const float sn = fmaf(uu, se[q], ww * ce[q]);
+            const float sq = fast_sqrt(fmaxf(1.f - sn, 0.f));
+            const float2 el = asin01_f32x2(f2(sn, sn), f2(sq, sq));
+            v *= fast_rcp(fmaf(hs, el.x, hc));
+          }
+          st_row(r0, jq[q], v);
         }
-        st_row(r0, jq[q], v);
       }
     }
-  }
+  };
+  if (!krj)
+    phase3(std::integral_constant<int, 0>{});
+  else if (s_cal_ie >= 0)
+    phase3(std::integral_constant<int, 2>{});
+  else
+    phase3(std::integral_constant<int, 1>{});
 }
 
 static size_t synth_f32_smem(int n_layers) {
