@@ -25,6 +25,9 @@
 #endif
 #define F32_W (F32_KT + 1 + 2 * F32_HALO)
 #define F32_NP (F32_DT / 2)  // detector pairs per tile
+#ifndef F32_KS
+#define F32_KS F32_NP  // float4 entries per knot row of ym4 (padding the rows by one entry was measured: no gain, 5.21 vs 5.09 ms)
+#endif
 #define F32_SPLN ((5 * F32_W + 3) & ~3)  // floats reserved for the spline system (keeps what follows 16-byte aligned)
 #ifndef F32_S
 #define F32_S 3  // full-rate samples per thread and iteration in phase 3 (4 spills at 80 registers)
@@ -256,7 +259,7 @@ __device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* 
           const int sl = slot0 + j;
           // times Mueller [0,0]; the spline being linear in the data, the detector gain goes in here too
           const float y = ok ? emission_blend_f32(P, dc_band[sl], ip, ie, wp, we) * dc_mu[sl] * dc_gain[sl] : r_nan<float>();
-          if (kb + q * NW < Wn) ymf[(kk[q] * F32_NP + (sl >> 1)) * 4 + (sl & 1)] = y;
+          if (kb + q * NW < Wn) ymf[(kk[q] * F32_KS + (sl >> 1)) * 4 + (sl & 1)] = y;
         }
       }
     }
@@ -270,7 +273,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   extern __shared__ __align__(16) unsigned char dyn[];
   float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_d0, y_d1, m_d0, m_d1}
   float* ymf = reinterpret_cast<float*>(dyn);
-  float4* splq = ym4 + F32_W * F32_NP;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
+  float4* splq = ym4 + F32_W * F32_KS;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
   float* h26 = reinterpret_cast<float*>(splq + F32_W);               // [W] h_k^2 / 6
   Knot<float>* knots = reinterpret_cast<Knot<float>*>(reinterpret_cast<float*>(splq) + F32_SPLN);
   LayerKnot<float>* lk = reinterpret_cast<LayerKnot<float>*>(knots + F32_W);  // [n_layers][W]
@@ -422,7 +425,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   // of ~300 and no warp idles at the barrier for long.
   {
     float* row = ymf + (lane >> 1) * 4 + (lane & 1);
-    constexpr int RS = F32_NP * 4;  // stride between knots, in floats
+    constexpr int RS = F32_KS * 4;  // stride between knots, in floats
     constexpr int NW = F32_THREADS / 32;
     const int lo = 1, hi = Wn - 2, nrows = hi - lo + 1;
     const int ka = lo + (nrows * warp) / NW, kb = lo + (nrows * (warp + 1)) / NW - 1;  // this warp's rows [ka, kb]
@@ -534,7 +537,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
           ce[q] = (float)bf.x;
           se[q] = (float)bf.y;
         }
-        yk[q] = ym4 + li * F32_NP;
+        yk[q] = ym4 + li * F32_KS;
         jq[q] = (int)j;
       }
 #pragma unroll 2
@@ -550,7 +553,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
         asm("" : "+l"(r0), "+l"(r1));  // keep the row pointers as they are: each store is then one mad.wide + one st
 #pragma unroll
         for (int q = 0; q < F32_S; q++) {
-          const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
+          const float4 q0 = yk[q][p], q1 = yk[q][F32_KS + p];
           const float a0 = 1.f - a1[q];
           float2 v = __fmul2_rn(f2(a0, a0), f2(q0.x, q0.y));
           v = __ffma2_rn(f2(a1[q], a1[q]), f2(q1.x, q1.y), v);
@@ -590,7 +593,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
         float* __restrict__ r0 = out + dc_row[2 * p];
 #pragma unroll
         for (int q = 0; q < F32_S; q++) {
-          const float4 q0 = yk[q][p], q1 = yk[q][F32_NP + p];
+          const float4 q0 = yk[q][p], q1 = yk[q][F32_KS + p];
           float v = fmaf(a3[q], q1.z, fmaf(a2[q], q0.z, fmaf(a1[q], q1.x, (1.f - a1[q]) * q0.x)));
           if constexpr (MODE == 1) {
             const float sn = fmaf(uu, se[q], ww * ce[q]);
@@ -622,6 +625,6 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
 }
 
 static size_t synth_f32_smem(int n_layers) {
-  return (size_t)F32_W * F32_NP * sizeof(float4) + F32_SPLN * sizeof(float) + F32_W * sizeof(Knot<float>) +
+  return (size_t)F32_W * F32_KS * sizeof(float4) + F32_SPLN * sizeof(float) + F32_W * sizeof(Knot<float>) +
          (size_t)n_layers * F32_W * sizeof(LayerKnot<float>);
 }
