@@ -61,6 +61,12 @@ __device__ __forceinline__ void st_row(float* row, int j, float v) {
   asm("mad.wide.s32 %0, %1, 4, %2;" : "=l"(a) : "r"(j), "l"(row));
   asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
 }
+// *(sample_ptr + row_bytes) = v: the per-thread pointer already holds out + j, the row offset is the tile's constant
+__device__ __forceinline__ void st_at(const char* sample_ptr, long long row_bytes, float v) {
+  const char* a;
+  asm("add.s64 %0, %1, %2;" : "=l"(a) : "l"(sample_ptr), "l"(row_bytes));
+  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
+}
 // asin on [-1, 1]: pi/2 - sqrt(1 - |x|) P7(|x|)  (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 rad)
 __device__ __forceinline__ float fast_asin(float x) {
   const float a = fabsf(x);
@@ -283,7 +289,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   __shared__ float dc_gain[F32_DT];
   __shared__ int dc_band[F32_DT];
   __shared__ float dc_mu[F32_DT];
-  __shared__ __align__(16) long long dc_row[F32_DT];  // element offset of each detector's output row
+  __shared__ __align__(16) long long dc_row[F32_DT];  // byte offset of each detector's output row
   __shared__ float4 dc_cal[F32_NP];  // {Hc_d0, Hc_d1, Hs_d0, Hs_d1}: the line H(el) of the tile's elevation interval (s_cal_ie >= 0)
   __shared__ int s_cal_ie;
 
@@ -345,7 +351,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     long long row = 0;
     if (dd < nd) {
       const int64_t d = order[dbase + dd];  // absolute detector index of this slot
-      row = (d - det0) * P.n_t;
+      row = (d - det0) * P.n_t * (long long)sizeof(float);
       u = (float)P.det_full[2 * d];
       w = (float)P.det_full[2 * d + 1];
       g = apply_gain ? (float)P.gain[d] : 1.f;
@@ -516,7 +522,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     for (int64_t jb = (j0 & ~(int64_t)31) + tid; jb < j1; jb += F32_THREADS * F32_S) {
       float a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
       const float4* yk[F32_S];
-      int jq[F32_S];
+      const char* oq[F32_S];  // out + j: a store is then one 64-bit add of the row's byte offset
 #pragma unroll
       for (int q = 0; q < F32_S; q++) {
         // a sample index outside the tile repeats the tile's first / last sample: the same value is stored to the same address
@@ -538,7 +544,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
           se[q] = (float)bf.y;
         }
         yk[q] = ym4 + li * F32_KS;
-        jq[q] = (int)j;
+        oq[q] = reinterpret_cast<const char*>(out + j);
       }
 #pragma unroll 2
       for (int p = 0; p < npairs; p++) {
@@ -548,9 +554,6 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
         if constexpr (MODE == 1) tb = dc_tab[p];
         if constexpr (MODE == 2) cal = dc_cal[p];
         const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
-        float* r0 = out + ro.x;
-        float* r1 = out + ro.y;
-        asm("" : "+l"(r0), "+l"(r1));  // keep the row pointers as they are: each store is then one mad.wide + one st
 #pragma unroll
         for (int q = 0; q < F32_S; q++) {
           const float4 q0 = yk[q][p], q1 = yk[q][F32_KS + p];
@@ -576,13 +579,13 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
             v = __fmul2_rn(v, f);
           } else if constexpr (MODE == 2) {
             const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
-            const float2 sq = f2(fast_sqrt(fmaxf(1.f - sn.x, 0.f)), fast_sqrt(fmaxf(1.f - sn.y, 0.f)));
+            const float2 sq = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));  // |.|: sin el may exceed 1 by an ulp
             const float2 el = asin01_f32x2(sn, sq);
             const float2 den = __ffma2_rn(f2(cal.z, cal.w), el, f2(cal.x, cal.y));
             v = __fmul2_rn(v, f2(fast_rcp(den.x), fast_rcp(den.y)));
           }
-          st_row(r0, jq[q], v.x);
-          st_row(r1, jq[q], v.y);
+          st_at(oq[q], ro.x, v.x);
+          st_at(oq[q], ro.y, v.y);
         }
       }
       if (nd & 1) {  // odd tail detector of a partial tile; the same arithmetic as the paired path (bit-identical shards)
@@ -590,7 +593,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
         const float uu = dc_uw[p].x, ww = dc_uw[p].z;
         const int tbx = dc_tab[p].x;
         const float hc = dc_cal[p].x, hs = dc_cal[p].z;
-        float* __restrict__ r0 = out + dc_row[2 * p];
+        const long long r0 = dc_row[2 * p];
 #pragma unroll
         for (int q = 0; q < F32_S; q++) {
           const float4 q0 = yk[q][p], q1 = yk[q][F32_KS + p];
@@ -607,11 +610,11 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
             v *= f;
           } else if constexpr (MODE == 2) {
             const float sn = fmaf(uu, se[q], ww * ce[q]);
-            const float sq = fast_sqrt(fmaxf(1.f - sn, 0.f));
+            const float sq = fast_sqrt(fabsf(1.f - sn));
             const float2 el = asin01_f32x2(f2(sn, sn), f2(sq, sq));
             v *= fast_rcp(fmaf(hs, el.x, hc));
           }
-          st_row(r0, jq[q], v);
+          st_at(oq[q], r0, v);
         }
       }
     }
