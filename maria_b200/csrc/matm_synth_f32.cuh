@@ -15,7 +15,11 @@
 #define F32_DT 32
 #define F32_THREADS 256
 #ifndef F32_KT
-#define F32_KT 128   // spline intervals per tile
+// spline intervals per tile.  Both per-tile loops are quantised: phase 1 works in passes of 8 M F32_G knots over the
+// KT + 1 + 2 HALO knots of the window, phase 3 in iterations of 256 F32_S samples over the KT U samples of the tile
+// (U = full-rate samples per interval).  135 fills both at the C4 cadence (U = 22.6: 156 knots = 2.5 passes of 64,
+// 3056 samples = 3.98 iterations of 768) and keeps three CTAs per SM; any value is correct (-DF32_KT=... retunes).
+#define F32_KT 135
 #endif
 #ifndef F32_HALO
 #define F32_HALO 10  // extra knots each side; the error of the artificial boundary decays as (2 - sqrt 3)^HALO
@@ -182,12 +186,15 @@ __device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* 
     const float pwv0 = (float)P.pwv0;
     int ip = 0, ie = 0;
     constexpr int NW = (F32_THREADS / 32) * M;
-    for (int kb = warp * M + sub; kb < Wn; kb += NW * F32_G) {
-      float dppx[F32_G], dppy[F32_G], sinel[F32_G], acc[F32_G];
-      int kk[F32_G];
+    // one pass = G knots per thread, NW * G knots per CTA.  Full passes use F32_G; what is left at the end of the window
+    // takes the smallest G that covers it, so a window of 148 knots costs 2.5 passes of 64 (M = 2) instead of 3.
+    auto pass = [&](auto gtag, const int kb) {
+      constexpr int G = decltype(gtag)::value;
+      float dppx[G], dppy[G], sinel[G], acc[G];
+      int kk[G];
       bool bad = false;
 #pragma unroll
-      for (int q = 0; q < F32_G; q++) {
+      for (int q = 0; q < G; q++) {
         kk[q] = min(kb + q * NW, Wn - 1);  // a short last group repeats the last knot (same value, same slot)
         const Knot<float> kc = knots[kk[q]];
         // direction of the detector minus direction of the boresight, horizon frame (coords/transforms.py:10-29)
@@ -209,10 +216,10 @@ __device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* 
         const float4 Dm = *reinterpret_cast<const float4*>(&ls[l].D0);
         const int4 Ln = *reinterpret_cast<const int4*>(&ls[l].rms);
         const float* data = ls[l].data;
-        float wx[F32_G], wy[F32_G];
-        const float* v[F32_G];
+        float wx[G], wy[G];
+        const float* v[G];
 #pragma unroll
-        for (int q = 0; q < F32_G; q++) {
+        for (int q = 0; q < G; q++) {
           const LayerKnot<float> b = lk[l * F32_W + kk[q]];
           const float fx = fmaf(Dm.x, dppx[q], fmaf(Dm.y, dppy[q], b.fx));
           const float fy = fmaf(Dm.z, dppx[q], fmaf(Dm.w, dppy[q], b.fy));
@@ -238,22 +245,22 @@ __device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* 
           }
           v[q] = data + (ix * Ln.w + iy);
         }
-        float v00[F32_G], v01[F32_G], v10[F32_G], v11[F32_G];
+        float v00[G], v01[G], v10[G], v11[G];
 #pragma unroll
-        for (int q = 0; q < F32_G; q++) {
+        for (int q = 0; q < G; q++) {
           v00[q] = __ldg(v[q]);
           v01[q] = __ldg(v[q] + 1);
           v10[q] = __ldg(v[q] + Ln.w);
           v11[q] = __ldg(v[q] + Ln.w + 1);
         }
 #pragma unroll
-        for (int q = 0; q < F32_G; q++) {
+        for (int q = 0; q < G; q++) {
           const float a = fmaf(wy[q], v01[q] - v00[q], v00[q]), bb = fmaf(wy[q], v11[q] - v10[q], v10[q]);
           acc[q] = fmaf(__int_as_float(Ln.x), fmaf(wx[q], bb - a, a), acc[q]);
         }
       }
 #pragma unroll
-      for (int q = 0; q < F32_G; q++) {
+      for (int q = 0; q < G; q++) {
         if (bad || ((badmask >> q) & 1)) {
           if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, wa + kk[q]);
           if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
@@ -267,6 +274,20 @@ __device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* 
           const float y = ok ? emission_blend_f32(P, dc_band[sl], ip, ie, wp, we) * dc_mu[sl] * dc_gain[sl] : r_nan<float>();
           if (kb + q * NW < Wn) ymf[(kk[q] * F32_KS + (sl >> 1)) * 4 + (sl & 1)] = y;
         }
+      }
+    };
+    const int vw = warp * M + sub;
+    for (int base = 0; base < Wn;) {
+      const int rem = Wn - base;
+      if (rem > (F32_G / 2) * NW) {
+        pass(std::integral_constant<int, F32_G>{}, base + vw);
+        base += F32_G * NW;
+      } else if (rem > NW) {
+        pass(std::integral_constant<int, F32_G / 2>{}, base + vw);
+        base += (F32_G / 2) * NW;
+      } else {
+        pass(std::integral_constant<int, 1>{}, base + vw);
+        base += NW;
       }
     }
   }
