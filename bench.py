@@ -40,7 +40,7 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--depth", type=int, default=2, help="realisations whose AR chains are in flight underneath the synthesis")
+    ap.add_argument("--depth", type=int, default=3, help="realisations whose AR chains are in flight underneath the synthesis")
     ap.add_argument("--no-overlap", action="store_true",
                     help="generate and synthesise strictly one after the other (default: the AR chains of realisation i+1 run "
                          "underneath the synthesis kernel of realisation i)")
