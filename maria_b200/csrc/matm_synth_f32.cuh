@@ -1,13 +1,15 @@
 // The production (float) instance of the fused synthesis kernel a6..a14, written for instruction count: the kernel is
-// issue-bound, not HBM-bound (ncu: ~140 thread-instructions per output sample in the generic template), so every
-// per-output-sample operation is stripped to the minimum and done on two detectors at once with the packed
-// fma.rn.f32x2 / mul / add instructions of sm_100.
+// issue- and data-pipe-bound, not HBM-bound (ncu: ~140 thread-instructions per output sample in the generic template,
+// ~37 here), so every per-output-sample operation is stripped to the minimum and done on two detectors at once with
+// the packed fma.rn.f32x2 / mul / add instructions of sm_100.
 //
-//   phase 1  loading [pW] at the window's knots; lane = detector, warps stride over knots          (per knot)
-//   phase 2  not-a-knot cubic spline second derivatives by the windowed Thomas sweep               (per knot)
-//   phase 3  spline evaluation + pW -> K_RJ at the full-rate samples; thread = sample, loop over   (per sample)
-//            detector PAIRS: 2 LDS.128 + 4 packed FMAs for the spline, and the calibration factor from the
-//            t = sqrt(1 - sin el) table of matm_setup.cu (no asin, no search, no divide).
+//   phase 1  loading [pW] at the window's knots; lane = focal-plane position (co-located detectors share the line of
+//            sight: tile multiplicity M), warps stride over knots, F32_G knots per thread                (per knot)
+//   phase 2  not-a-knot cubic spline second derivatives by the windowed Thomas sweep                     (per knot)
+//   phase 3  spline evaluation + pW -> K_RJ at the full-rate samples; thread = F32_S samples, loop over   (per sample)
+//            detector PAIRS: 2 LDS.128 + 4 packed FMAs for the spline; the calibration factor is
+//            rcp(Hc + Hs asin(sin el)) in packed arithmetic when the tile lies in one interval of the elevation
+//            grid, else the t = sqrt(1 - sin el) table of matm_setup.cu (no search, no divide).
 #pragma once
 #include <type_traits>
 #include "matm_synth.cuh"
@@ -58,12 +60,6 @@ __device__ __forceinline__ float fast_rcp(float x) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
-}
-// row[j] = v with the address formed by one mad.wide (the compiler otherwise re-associates it into six instructions)
-__device__ __forceinline__ void st_row(float* row, int j, float v) {
-  float* a;
-  asm("mad.wide.s32 %0, %1, 4, %2;" : "=l"(a) : "r"(j), "l"(row));
-  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
 }
 // *(sample_ptr + row_bytes) = v: the per-thread pointer already holds out + j, the row offset is the tile's constant
 __device__ __forceinline__ void st_at(const char* sample_ptr, long long row_bytes, float v) {
