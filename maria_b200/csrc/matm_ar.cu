@@ -393,7 +393,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
   }
 }
 
-template <int L, int MP>
+template <int L, int MP, int MC = -1>  // MC >= 0: the LATE part is registers [0, 4 MC), fixed at compile time
 __global__ void __launch_bounds__(AR_THREADS, 1)
     ar_chain_v4_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
                        double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl) {
@@ -446,7 +446,8 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   const int n1 = cnt[0], n2 = cnt[1], n3 = cnt[2];
   // registers [0, mcrit) hold every offset-1 sample (the samples are sorted by offset): the part of the dot product that
   // has to wait for the row just produced; the rest is computed one step ahead
-  const int mcrit = min(MP, 4 * ((n1 + 4 * L - 1) / (4 * L)));
+  // (with MC given by the host from n_cs >= n1, the unrolled groups carry no branch and their loads are batched)
+  const int mcrit = MC >= 0 ? min(MP, 4 * MC) : min(MP, 4 * ((n1 + 4 * L - 1) / (4 * L)));
   int p1 = -1, p2 = -1, p3 = -1;
   if (has_row && sub == 0) {
     p1 = pos[row0 + r];
@@ -503,7 +504,7 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
     double e0 = 0.0, e1 = 0.0, e2 = 0.0, e3 = 0.0;
 #pragma unroll
     for (int m = 0; m < MP; m += 4)
-      if (m >= mcrit) {
+      if (MC >= 0 ? (m >= 4 * MC) : (m >= mcrit)) {
         e0 = fma(a[m], g[L * m], e0);
         if (m + 1 < MP) e1 = fma(a[m + 1], g[L * (m + 1)], e1);
         if (m + 2 < MP) e2 = fma(a[m + 2], g[L * (m + 2)], e2);
@@ -527,7 +528,7 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
       double acc0 = pre, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
       for (int m = 0; m < MP; m += 4)
-        if (m < mcrit) {
+        if (MC >= 0 ? (m < 4 * MC) : (m < mcrit)) {
           acc0 = fma(a[m], g[L * m], acc0);
           if (m + 1 < MP) acc1 = fma(a[m + 1], g[L * (m + 1)], acc1);
           if (m + 2 < MP) acc2 = fma(a[m + 2], g[L * (m + 2)], acc2);
@@ -592,6 +593,14 @@ static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, cons
   }
   const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16;
   auto kernel = use_v3 ? ar_chain_v3_kernel<L, MP> : ar_chain_v4_kernel<L, MP>;
+  if constexpr (L == 8 && MP >= 32) if (!use_v3) {
+    // the long chains (n_cs ~ 100-160): the split between the LATE and EARLY registers as a compile-time constant.
+    // n_cs bounds the number of offset-1 samples from above, so registers [0, 4 mc) always hold all of them.
+    const int mc = (n_cs + 4 * L - 1) / (4 * L);
+    if (mc == 3) kernel = ar_chain_v4_kernel<L, MP, 3>;
+    if (mc == 4) kernel = ar_chain_v4_kernel<L, MP, 4>;
+    if (mc == 5) kernel = ar_chain_v4_kernel<L, MP, 5>;
+  }
   MATM_CUDA(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cl, 1, 1);
