@@ -10,6 +10,8 @@
 #include <cooperative_groups.h>
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "matm_common.cuh"
 
 namespace cg = cooperative_groups;
@@ -393,7 +395,8 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
   }
 }
 
-template <int L, int MP, int MC = -1>  // MC >= 0: the LATE part is registers [0, 4 MC), fixed at compile time
+// MC >= 0: the LATE part is registers [0, 4 MC), fixed at compile time; CL > 0: the cluster size, fixed at compile time
+template <int L, int MP, int MC = -1, int CL = 0>
 __global__ void __launch_bounds__(AR_THREADS, 1)
     ar_chain_v4_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
                        double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl) {
@@ -518,11 +521,14 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   if (active) {
     pre = early_part(i_top);
 
-    auto step = [&](const int i, double(&fs)[2], double& bz) {
+    // GD = false: the steady state (i >= 5), where every "does that step exist" test below is true
+    auto step = [&](auto guard, const int i, double(&fs)[2], double& bz) {
+      constexpr bool GD = decltype(guard)::value;
+      const int ncl = CL > 0 ? CL : cl;
       const uint32_t par = ((i_top - i) >> 2) & 1;
       // (1) the row just produced has landed in G[i]
       mbar_wait_cluster(bars_s + 8 * (i & 3), par);
-      if (tid == 0 && i >= 4) mbar_arm(bars_s + 8 * (i & 3), late_full);
+      if (tid == 0 && (!GD || i >= 4)) mbar_arm(bars_s + 8 * (i & 3), late_full);
       // (2) the LATE part of the dot product
       const double* g = G + (i & 3) * gs + sub;
       double acc0 = pre, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
@@ -544,39 +550,46 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
         const uint32_t d2 = G_s + 8u * (((i - 2) & 3) * gs + p2), b2 = bars_s + 8u * (4 + ((i - 2) & 3));
         const uint32_t d3 = G_s + 8u * (((i - 3) & 3) * gs + p3), b3 = bars_s + 8u * (4 + ((i - 3) & 3));
         buffer[(size_t)i * n_cs + row0 + r] = v;  // read again (far samples) no sooner than three steps from now
-        for (int c = 0; c < cl; c++) {
-          if (p1 >= 0 && i >= 1) st_async_f64(mapa_u32(d1, c), v, mapa_u32(b1, c));
-          if (p2 >= 0 && i >= 2) st_async_f64(mapa_u32(d2, c), v, mapa_u32(b2, c));
-          if (p3 >= 0 && i >= 3) st_async_f64(mapa_u32(d3, c), v, mapa_u32(b3, c));
+#pragma unroll
+        for (int c = 0; c < (CL > 0 ? CL : 8); c++) {
+          if (c >= ncl) break;
+          if (p1 >= 0 && (!GD || i >= 1)) st_async_f64(mapa_u32(d1, c), v, mapa_u32(b1, c));
+          if (p2 >= 0 && (!GD || i >= 2)) st_async_f64(mapa_u32(d2, c), v, mapa_u32(b2, c));
+          if (p3 >= 0 && (!GD || i >= 3)) st_async_f64(mapa_u32(d3, c), v, mapa_u32(b3, c));
         }
       }
       // (4) off the critical path: send the far values of step i - 2 (in flight since step i + 4), re-issue the set for
       //     step i - 4 (rows >= i + 1, complete: their LATE barrier was passed above), re-issue B z for step i - 2
-      if (i >= 2) {
+      if (!GD || i >= 2) {
         const uint32_t be = mapa_u32(bars_s + 8u * (4 + ((i - 2) & 3)), cta);
 #pragma unroll
         for (int q = 0; q < 2; q++)
           if (foff[q] >= 0)
             st_async_f64(mapa_u32(G_s + 8u * (((i - 2) & 3) * gs + n_near + tid + q * AR_THREADS), cta), fs[q], be);
       }
-      if (i >= 4) {
+      if (!GD || i >= 4) {
 #pragma unroll
         for (int q = 0; q < 2; q++)
           if (foff[q] >= 0) fs[q] = __ldcg(buffer + (size_t)(i - 4) * n_cs + foff[q]);
       }
-      if (i >= 2 && has_row) bz = __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r);
+      if ((!GD || i >= 2) && has_row) bz = __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r);
       // (5) the EARLY part of step i - 1, while the row of step i is on its way
-      if (i >= 1) {
+      if (!GD || i >= 1) {
         const uint32_t pe = ((i_top - (i - 1)) >> 2) & 1;
         mbar_wait_cluster(bars_s + 8 * (4 + ((i - 1) & 3)), pe);
-        if (tid == 0 && i - 1 >= 4) mbar_arm(bars_s + 8 * (4 + ((i - 1) & 3)), early_full);
+        if (tid == 0 && (!GD || i - 1 >= 4)) mbar_arm(bars_s + 8 * (4 + ((i - 1) & 3)), early_full);
         pre = early_part(i - 1);
       }
     };
 
-    for (int i = i_top; i >= 1; i -= 2) {  // i_top = 2 n_ext - 1 is odd
-      step(i, far_s[1], bz_s[1]);
-      step(i - 1, far_s[0], bz_s[0]);
+    int i = i_top;  // 2 n_ext - 1: odd
+    for (; i >= 7; i -= 2) {
+      step(std::false_type{}, i, far_s[1], bz_s[1]);
+      step(std::false_type{}, i - 1, far_s[0], bz_s[0]);
+    }
+    for (; i >= 1; i -= 2) {
+      step(std::true_type{}, i, far_s[1], bz_s[1]);
+      step(std::true_type{}, i - 1, far_s[0], bz_s[0]);
     }
   }
   // no CTA may leave while values are still on their way to it
@@ -598,8 +611,8 @@ static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, cons
     // n_cs bounds the number of offset-1 samples from above, so registers [0, 4 mc) always hold all of them.
     const int mc = (n_cs + 4 * L - 1) / (4 * L);
     if (mc == 3) kernel = ar_chain_v4_kernel<L, MP, 3>;
-    if (mc == 4) kernel = ar_chain_v4_kernel<L, MP, 4>;
-    if (mc == 5) kernel = ar_chain_v4_kernel<L, MP, 5>;
+    if (mc == 4) kernel = cl == 2 ? ar_chain_v4_kernel<L, MP, 4, 2> : ar_chain_v4_kernel<L, MP, 4>;
+    if (mc == 5) kernel = cl == 3 ? ar_chain_v4_kernel<L, MP, 5, 3> : ar_chain_v4_kernel<L, MP, 5>;
   }
   MATM_CUDA(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
