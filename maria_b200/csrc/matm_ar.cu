@@ -457,6 +457,22 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
     p2 = pos[n_cs + row0 + r];
     p3 = pos[2 * n_cs + row0 + r];
   }
+  // With the cluster size known at compile time the 3 CL destinations of a value are spread over the L lanes of its row
+  // (after the butterfly every lane holds the sum): lane `sub` sends to (CTA t / 3, gather vector of step i - 1 - t % 3)
+  // for t = sub and t = sub + L.
+  constexpr bool SPREAD = CL > 0 && 3 * CL <= 2 * L;
+  uint32_t pubd[2] = {0, 0}, pubb[2] = {0, 0};
+  int pubk[2] = {0, 0};
+  if (SPREAD) {
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      const int t = sub + j * L, c = min(t / 3, cl - 1), k = t % 3 + 1;
+      const int pk = (has_row && t < 3 * cl) ? pos[(k - 1) * n_cs + row0 + r] : -1;
+      pubk[j] = pk >= 0 ? k : 0;
+      pubd[j] = mapa_u32(G_s, c) + 8u * max(pk, 0);
+      pubb[j] = mapa_u32(bars_s, c) + (k == 1 ? 0u : 32u);
+    }
+  }
   // ---- prologue: the initial-noise rows i_top+1 .. i_top+3 feed steps i_top, i_top-1, i_top-2 ----
   for (int e = tid; e < 3 * n_near; e += AR_THREADS) {
     const int k = e / n_near, s = e % n_near;  // step i_top - k, near sample s
@@ -544,6 +560,16 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
 #pragma unroll
       for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
       // (3) publish row r of step i into the gather vectors of steps i-1, i-2, i-3 of every CTA, and to global memory
+      if (SPREAD) {
+        const double v = bz + acc;
+        if (has_row && sub == 0) buffer[(size_t)i * n_cs + row0 + r] = v;  // read again (far samples) three steps from now at the earliest
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+          if (j == 1 && 3 * CL <= L) break;
+          const int bsel = (i - pubk[j]) & 3;
+          if (pubk[j] != 0 && (!GD || i >= pubk[j])) st_async_f64(pubd[j] + 8u * (bsel * gs), v, pubb[j] + 8u * bsel);
+        }
+      } else
       if (has_row && sub == 0) {
         const double v = bz + acc;
         const uint32_t d1 = G_s + 8u * (((i - 1) & 3) * gs + p1), b1 = bars_s + 8u * ((i - 1) & 3);
