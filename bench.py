@@ -41,6 +41,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--depth", type=int, default=3, help="realisations whose AR chains are in flight underneath the synthesis")
+    ap.add_argument("--chunk-mib", type=int, default=None, help="scratch per detector chunk of the two-kernel synthesis [MiB]")
+    ap.add_argument("--chunk-serial", action="store_true", help="run the detector chunks of one synthesis on one stream")
     ap.add_argument("--no-overlap", action="store_true",
                     help="generate and synthesise strictly one after the other (default: the AR chains of realisation i+1 run "
                          "underneath the synthesis kernel of realisation i)")
@@ -227,6 +229,8 @@ def run_b200(args):
     gain = np.exp(dets.gain_error * np.random.standard_normal(size=dets.n))  # simulation.py:239-241
     atm.set_gain(gain)
     out = ctx.empty((n_det, n_t))  # the TOD shard, resident in HBM (72 GB at full size)
+    if args.chunk_mib is not None or args.chunk_serial:
+        ctx.check(ctx.lib.matm_set_tuning(ctx.h, args.chunk_mib or 32, 0 if args.chunk_serial else 1))
 
     overlap = not args.no_overlap
 

@@ -128,6 +128,11 @@ int matm_upsample_linear(matm_handle* h, const double* in_dev, int64_t n_det, do
 int matm_synthesize(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, int units, int apply_gain,
                     void* stream);
 
+/* Tuning of the float path of matm_synthesize: it runs per chunk of detector tiles as two kernels (loading at the
+ * atmosphere-rate knots into a scratch of `chunk_mib` MiB, then spline + evaluation + calibration at the full rate);
+ * overlap != 0 alternates consecutive chunks between two scratch buffers and two internal streams.  Defaults: 32, 1. */
+int matm_set_tuning(matm_handle* h, int chunk_mib, int overlap);
+
 /* Same, delivering into HOST memory (pinned or pageable): detector-chunked, device->host copies overlapped with
  * the kernels of the next chunk.  Synchronises before returning. */
 int matm_synthesize_host(matm_handle* h, int64_t det0, int64_t n_det, void* out_host, int units, int apply_gain);

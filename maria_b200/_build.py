@@ -9,7 +9,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libmaria_atm.so")
 SOURCES = ["matm_core.cu", "matm_ar.cu", "matm_smooth.cu", "matm_setup.cu", "matm_synth.cu"]
-HEADERS = ["matm_common.cuh", "matm_synth.cuh", os.path.join("..", "..", "include", "maria_atm.h")]
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join("..", "..", "include", "maria_atm.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--use_fast_math=false",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 

@@ -39,10 +39,18 @@ struct SynthParams {
   const double* t_atm;     // (n_t_atm,): the knot times exactly as np.arange produced them
   const double* spl;       // (n_t_atm, 5): not-a-knot cubic spline system in units of `timestep`:
                            //   [0] 1/h_k  [1] h_k^2/6 (interval k);  [2] w_k  [3] a_k w_k  [4] c'_k (row k, Thomas)
+  const double* el_full;   // (n_t,): boresight elevation at the full rate
+  const double* el_rng;    // (n_t_atm, 2): min / max of el_full over the samples of spline interval k (+inf / -inf if empty)
+  const float4* knot_f;    // (n_t_atm,): bore_atm in float (fp32 handles)
+  const float4* samp_w;    // (n_t,): {a1, a2, a3, bits of the interval index i}: cubic-spline weights of the full-rate sample,
+                           //   value = y_i + a1 (y_i+1 - y_i) + a2 M_i + a3 M_i+1  (sample_weights_kernel)
+  const void* lk_tab;      // (n_layers, n_t_atm) LayerKnot<float>: boresight cell + fraction in every layer grid (fp32 handles)
   // detectors
   int64_t n_det;
   const double* det_atm;   // (n_det, 4): u, Y, w-1, unused   with the atmosphere's offsets
   const double* det_full;  // (n_det, 2): u, w                with the rolled offsets
+  const double* det_cal;   // (n_det, 2): beta, eps with u = (1 - eps) sin beta, w = (1 - eps) cos beta, i.e.
+                           //   sin el_d = (1 - eps) sin(el_b - beta)
   const int32_t* band_index;
   const double* mueller00;
   const double* gain;
@@ -67,6 +75,7 @@ struct SynthParams {
   int calq_n;
   float pwv_lo_f, pwv_hi_f, el_lo_f, el_hi_f;  // ends of the fp32 (pwv, el) grids
   float det_rmax_f;        // largest angular distance of a detector (rolled offsets) from the boresight [rad]
+  double det_rmax;
   int table_ok;            // 0 if T0 / cal_T0 / cal_pwv left the table (results are NaN, as the reference)
   int* flags;              // [0] = status bits, [1] = layer, [2..3] = det (lo, hi), [4..5] = sample (lo, hi)
 };
@@ -82,7 +91,18 @@ struct matm_handle {
   // owned device arrays
   double *bore_atm = nullptr, *bore_full = nullptr, *t_full = nullptr;
   int64_t* jstart = nullptr;
-  double *t_atm = nullptr, *spl = nullptr;
+  double *t_atm = nullptr, *spl = nullptr, *el_full = nullptr, *el_rng = nullptr, *det_cal = nullptr;
+  float4* knot_f = nullptr;
+  float4* samp_w = nullptr;
+  void* lk_tab = nullptr;
+  // atmosphere-rate loading of the detector chunks in flight (fp32 production path): [tile][knot][32 slots]
+  float* yk_buf[2] = {nullptr, nullptr};
+  size_t yk_bytes = 0;
+  bool yk_used = false;
+  int chunk_mib = 32;   // scratch per chunk; two chunks in flight must fit the 126 MB L2 next to the layers
+  bool overlap = true;  // alternate chunks between two side streams
+  cudaStream_t yk_stream[2] = {nullptr, nullptr};
+  cudaEvent_t yk_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double* layer_base[MATM_MAX_LAYERS] = {};
   double *det_atm = nullptr, *det_full = nullptr, *mueller00 = nullptr, *gain = nullptr;
   int32_t* band_index = nullptr;

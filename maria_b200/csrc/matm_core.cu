@@ -37,6 +37,18 @@ extern "C" int matm_destroy(matm_handle* h) {
   cudaFree(h->jstart);
   cudaFree(h->t_atm);
   cudaFree(h->spl);
+  cudaFree(h->el_full);
+  cudaFree(h->el_rng);
+  cudaFree(h->knot_f);
+  cudaFree(h->samp_w);
+  cudaFree(h->lk_tab);
+  cudaFree(h->det_cal);
+  for (int i = 0; i < 2; i++) {
+    cudaFree(h->yk_buf[i]);
+    if (h->yk_stream[i]) cudaStreamDestroy(h->yk_stream[i]);
+  }
+  for (int i = 0; i < 4; i++)
+    if (h->yk_ev[i]) cudaEventDestroy(h->yk_ev[i]);
   for (int l = 0; l < MATM_MAX_LAYERS; l++) cudaFree(h->layer_base[l]);
   cudaFree(h->det_atm);
   cudaFree(h->det_full);

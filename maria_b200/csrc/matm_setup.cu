@@ -56,6 +56,41 @@ __global__ void jstart_kernel(const double* __restrict__ t, int64_t n_t, double 
   jstart[k] = lo;
 }
 
+// el_rng[k] = (min, max) of the full-rate boresight elevation over the samples of spline interval k, i.e.
+// [jstart[k], jstart[k + 1]): what the per-tile choice of the a14 evaluation mode has to bound (the elevation at the
+// knots does not bound the full-rate samples at turnarounds or in the extrapolated tail).
+__global__ void el_range_kernel(const double* __restrict__ el, const int64_t* __restrict__ jstart, int n_int,
+                                double* __restrict__ rng) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_int) return;
+  double lo = INFINITY, hi = -INFINITY;
+  for (int64_t j = jstart[k]; j < jstart[k + 1]; j++) {
+    lo = fmin(lo, el[j]);
+    hi = fmax(hi, el[j]);
+  }
+  rng[2 * k] = lo;
+  rng[2 * k + 1] = hi;
+}
+
+// Per full-rate sample: the interval i of the knot vector it falls in (the same rule as jstart) and the weights of the
+// cubic spline in its second-derivative form, s = (t - x_i) / h_i:
+//   S(t) = (1 - s) y_i + s y_i+1 + h_i^2/6 [((1-s)^3 - (1-s)) M_i + (s^3 - s) M_i+1]      (M in units of timestep^-2)
+// evaluated in float64 and rounded once; they depend on the time axes only, so every tile of every detector reads them.
+__global__ void sample_weights_kernel(const double* __restrict__ t, int64_t n_t, const double* __restrict__ x, double t0,
+                                      double ts, int n_atm, float4* __restrict__ out) {
+  int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_t) return;
+  const int i = interval_of(t[j], t0, ts, n_atm);
+  const double h = x[i + 1] - x[i], s = (t[j] - x[i]) / h, c = 1.0 - s, hk = h / ts, h26 = hk * hk / 6.0;
+  out[j] = make_float4((float)s, (float)(h26 * (c * c * c - c)), (float)(h26 * (s * s * s - s)), __int_as_float(i));
+}
+
+__global__ void knot_f_kernel(const double* __restrict__ bore_atm, int n, float4* __restrict__ out) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  out[k] = make_float4((float)bore_atm[4 * k], (float)bore_atm[4 * k + 1], (float)bore_atm[4 * k + 2], (float)bore_atm[4 * k + 3]);
+}
+
 // Not-a-knot cubic spline through the knots x_k (scipy interp1d kind="cubic" = make_interp_spline k=3, default
 // boundary condition; sim/atmosphere.py:73-80), as the tridiagonal system for the second derivatives M_k in units of
 // `timestep`: rows k = 1 .. n-2,  a_k M_{k-1} + b_k M_k + c_k M_{k+1} = 6 [(y_{k+1}-y_k)/h_k - (y_k-y_{k-1})/h_{k-1}],
@@ -108,11 +143,15 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_ho
   if (n_t > (int64_t)INT32_MAX) MATM_FAIL_ARG(h, "matm_set_scan: more than 2^31 - 1 samples per detector; split the scan in time");
   (void)az_host;  // the full-rate azimuth does not enter the path (only the elevation does, tod.py:126-133)
   const double t_atm0 = t_atm_host[0];
-  double *az_d = nullptr, *el_d = nullptr, *elf_d = nullptr;
+  double *az_d = nullptr, *el_d = nullptr;
   int rc;
   if ((rc = matm_upload(h, &az_d, az_atm_host, (size_t)n_t_atm))) return rc;
   if ((rc = matm_upload(h, &el_d, el_atm_host, (size_t)n_t_atm))) return rc;
-  if ((rc = matm_upload(h, &elf_d, el_host, (size_t)n_t))) return rc;
+  if ((rc = matm_upload(h, &h->el_full, el_host, (size_t)n_t))) return rc;
+  if ((rc = matm_upload(h, &h->el_rng, (const double*)nullptr, (size_t)n_t_atm * 2))) return rc;
+  if ((rc = matm_upload(h, &h->knot_f, (const float4*)nullptr, (size_t)n_t_atm))) return rc;
+  if ((rc = matm_upload(h, &h->samp_w, (const float4*)nullptr, (size_t)n_t))) return rc;
+  double* elf_d = h->el_full;
   if ((rc = matm_upload(h, &h->bore_atm, (const double*)nullptr, (size_t)n_t_atm * 4))) return rc;
   if ((rc = matm_upload(h, &h->bore_full, (const double*)nullptr, (size_t)n_t * 2))) return rc;
   if ((rc = matm_upload(h, &h->t_full, t_host, (size_t)n_t))) return rc;
@@ -129,10 +168,15 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_ho
     spline_coef_kernel<<<1, 32>>>(h->t_atm, n_t_atm, timestep, h->spl);
     MATM_LAUNCHED(h);
   }
+  el_range_kernel<<<(n_t_atm - 1 + 255) / 256, 256>>>(h->el_full, h->jstart, n_t_atm - 1, h->el_rng);
+  MATM_LAUNCHED(h);
+  knot_f_kernel<<<(n_t_atm + 255) / 256, 256>>>(h->bore_atm, n_t_atm, h->knot_f);
+  MATM_LAUNCHED(h);
+  sample_weights_kernel<<<(unsigned)((n_t + 255) / 256), 256>>>(h->t_full, n_t, h->t_atm, t_atm0, timestep, n_t_atm, h->samp_w);
+  MATM_LAUNCHED(h);
   MATM_CUDA(h, cudaDeviceSynchronize());
   cudaFree(az_d);
   cudaFree(el_d);
-  cudaFree(elf_d);
   SynthParams& P = h->P;
   P.n_t_atm = n_t_atm;
   P.n_t = n_t;
@@ -151,6 +195,10 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_ho
   }
   P.t_atm = h->t_atm;
   P.spl = h->spl;
+  P.el_full = h->el_full;
+  P.el_rng = h->el_rng;
+  P.knot_f = h->knot_f;
+  P.samp_w = h->samp_w;
   h->have_scan = true;
   h->have_layers = false;  // layer bases depend on the scan
   return MATM_OK;
@@ -184,6 +232,26 @@ __global__ void layer_base_kernel(const double* __restrict__ bore_atm, const dou
   }
 }
 
+// the boresight's position in a layer grid split into integer cell + fraction, in float (the fp32 loading kernel reads
+// one 16-byte record per layer and knot)
+struct LayerKnotF {
+  int ix, iy;
+  float fx, fy;
+};
+__global__ void lk_tab_kernel(const double* __restrict__ base, int n, LayerKnotF* __restrict__ out) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const double cx = base[2 * k], cy = base[2 * k + 1];
+  // clamp the integer part so that absurd (far out-of-grid) positions cannot overflow; they are flagged by the sampler
+  const double flx = fmin(fmax(floor(cx), -1.0e9), 1.0e9), fly = fmin(fmax(floor(cy), -1.0e9), 1.0e9);
+  LayerKnotF o;
+  o.ix = (int)flx;
+  o.iy = (int)fly;
+  o.fx = (float)(cx - flx);
+  o.fy = (float)(cy - fly);
+  out[k] = o;
+}
+
 extern "C" int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_desc* L, double pwv0) {
   MATM_CHECK_HANDLE(h);
   if (matm_set_device(h)) return MATM_ERR_CUDA;
@@ -193,6 +261,10 @@ extern "C" int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_de
   const int n = P.n_t_atm;
   double *vx_d = nullptr, *vy_d = nullptr, *T_d = nullptr;
   int rc;
+  if (h->lk_tab) MATM_CUDA(h, cudaFree(h->lk_tab));
+  h->lk_tab = nullptr;
+  if (n_layers > 0) MATM_CUDA(h, cudaMalloc(&h->lk_tab, (size_t)n_layers * n * sizeof(LayerKnotF)));
+  P.lk_tab = h->lk_tab;
   for (int l = 0; l < n_layers; l++) {
     const matm_layer_desc& d = L[l];
     if (!d.data_dev || d.n_ext < 2 || d.n_cs < 2 || !d.vx_host || !d.vy_host || !(d.ext_step > 0) || !(d.cs_last > d.cs0))
@@ -204,6 +276,8 @@ extern "C" int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_de
     const double cs_step = (d.cs_last - d.cs0) / (d.n_cs - 1);
     layer_base_kernel<<<1, 256>>>(h->bore_atm, vx_d, vy_d, n, P.timestep, d.h, T_d, d.ext0, d.ext_step, d.cs0, cs_step,
                                   h->layer_base[l]);
+    MATM_LAUNCHED(h);
+    lk_tab_kernel<<<(n + 255) / 256, 256>>>(h->layer_base[l], n, (LayerKnotF*)h->lk_tab + (size_t)l * n);
     MATM_LAUNCHED(h);
     MATM_CUDA(h, cudaDeviceSynchronize());
     LayerDev& o = P.layers[l];
@@ -228,7 +302,7 @@ extern "C" int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_de
 
 // ---- detectors -------------------------------------------------------------------------------------------
 __global__ void det_kernel(const double* __restrict__ off_atm, const double* __restrict__ off_full, int64_t n,
-                           double* __restrict__ det_atm, double* __restrict__ det_full) {
+                           double* __restrict__ det_atm, double* __restrict__ det_full, double* __restrict__ det_cal) {
   int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= n) return;
   {
@@ -245,8 +319,17 @@ __global__ void det_kernel(const double* __restrict__ off_atm, const double* __r
   {
     double dx = off_full[2 * d], dy = off_full[2 * d + 1];
     double r = sqrt(dx * dx + dy * dy), p = atan2(-dx, -dy);
-    det_full[2 * d + 0] = sin(r) * cos(p);
-    det_full[2 * d + 1] = cos(r);
+    double sr, cr, sp, cp;
+    sincos(r, &sr, &cr);
+    sincos(p, &sp, &cp);
+    const double u = sr * cp, w = cr;
+    det_full[2 * d + 0] = u;
+    det_full[2 * d + 1] = w;
+    // sin el_d = u sin(e) + w cos(e), e = el_b - pi/2, = rho sin(el_b - beta) with rho e^{i beta} = w + i u;
+    // 1 - rho = (sin r sin p)^2 / (1 + rho) without cancellation
+    const double rho = sqrt(u * u + w * w), q = sr * sp;
+    det_cal[2 * d + 0] = atan2(u, w);
+    det_cal[2 * d + 1] = q * q / (1.0 + rho);
   }
 }
 
@@ -275,6 +358,7 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   if ((rc = matm_upload(h, &of, offsets_full_host, (size_t)n_det * 2))) return rc;
   if ((rc = matm_upload(h, &h->det_atm, (const double*)nullptr, (size_t)n_det * 4))) return rc;
   if ((rc = matm_upload(h, &h->det_full, (const double*)nullptr, (size_t)n_det * 2))) return rc;
+  if ((rc = matm_upload(h, &h->det_cal, (const double*)nullptr, (size_t)n_det * 2))) return rc;
   if ((rc = matm_upload(h, &h->band_index, band_index_host, (size_t)n_det))) return rc;
   if ((rc = matm_upload(h, &h->mueller00, mueller00_host, (size_t)n_det))) return rc;
   std::vector<double> ones;
@@ -283,7 +367,7 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
     gain_host = ones.data();
   }
   if ((rc = matm_upload(h, &h->gain, gain_host, (size_t)n_det))) return rc;
-  det_kernel<<<(unsigned)((n_det + 255) / 256), 256>>>(oa, of, n_det, h->det_atm, h->det_full);
+  det_kernel<<<(unsigned)((n_det + 255) / 256), 256>>>(oa, of, n_det, h->det_atm, h->det_full, h->det_cal);
   MATM_LAUNCHED(h);
   MATM_CUDA(h, cudaDeviceSynchronize());
   cudaFree(oa);
@@ -299,6 +383,8 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   double rmax = 0.0;
   for (int64_t i = 0; i < n_det; i++) rmax = fmax(rmax, hypot(offsets_full_host[2 * i], offsets_full_host[2 * i + 1]));
   P.det_rmax_f = (float)(rmax * (1.0 + 1e-6));
+  P.det_rmax = rmax;
+  P.det_cal = h->det_cal;
   P.n_det = n_det;
   P.det_atm = h->det_atm;
   P.det_full = h->det_full;

@@ -1,7 +1,5 @@
 // The detector x time stages: a6/a7/a9 (line-of-sight sampling), a10 (linear upsample), and the fused
 // a6..a14 synthesis kernel (sampling -> emission lookup -> cubic not-a-knot upsample -> gain -> pW->K_RJ).
-#include <stdlib.h>
-
 #include "matm_synth.cuh"
 #include "matm_synth_f32.cuh"
 
@@ -280,6 +278,73 @@ static size_t synth_smem(int n_layers) {
          (size_t)n_layers * T::W * sizeof(LayerKnot<R>);
 }
 
+// The production float path: per chunk of detector tiles, loading_f32_kernel (atmosphere rate) writes the chunk's
+// loading at the knots into an L2-sized scratch, synth_eval_f32_kernel turns it into the full-rate TOD rows.  Consecutive
+// chunks alternate between two scratch buffers and two side streams, so that the latency-bound loading kernel of chunk
+// c + 1 fills the SMs the HBM-bound evaluation kernel of chunk c leaves idle; the caller's stream forks into them and
+// joins at the end (everything stays stream-ordered for the caller, nothing synchronises).
+static int launch_synth_f32(matm_handle* h, int64_t det0, int64_t n_det, float* out, int units, int apply_gain,
+                            cudaStream_t st) {
+  const SynthParams& P = h->P;
+  const int n = P.n_t_atm;
+  const int32_t* order = nullptr;
+  const uint8_t* tile_m = nullptr;
+  int rc = matm_detector_order(h, det0, n_det, &order, &tile_m);
+  if (rc) return rc;
+  const int64_t n_tiles = (n_det + F32_DT - 1) / F32_DT;
+  const size_t tile_bytes = (size_t)n * F32_DT * sizeof(float);
+  int64_t chunk = (int64_t)(((size_t)h->chunk_mib << 20) / tile_bytes);
+  if (chunk < 1) chunk = 1;
+  if (chunk > n_tiles) chunk = n_tiles;
+  const int n_kb = (n + LD_KA - 1) / LD_KA, n_tt = (n - 1 + F32_KT - 1) / F32_KT;
+  if (chunk * (int64_t)max(n_kb, n_tt) > INT32_MAX) chunk = INT32_MAX / max(n_kb, n_tt);
+  const size_t need = (size_t)chunk * tile_bytes;
+  const int64_t n_chunks = (n_tiles + chunk - 1) / chunk;
+  const bool two = h->overlap && n_chunks > 1;
+  if (h->yk_bytes < need) {
+    MATM_CUDA(h, cudaDeviceSynchronize());  // kernels of an earlier call may still read the old scratch
+    for (int i = 0; i < 2; i++) {
+      if (h->yk_buf[i]) MATM_CUDA(h, cudaFree(h->yk_buf[i]));
+      h->yk_buf[i] = nullptr;
+      MATM_CUDA(h, cudaMalloc((void**)&h->yk_buf[i], need));
+    }
+    h->yk_bytes = need;
+  }
+  for (int i = 0; i < 2; i++)
+    if (!h->yk_stream[i]) MATM_CUDA(h, cudaStreamCreateWithFlags(&h->yk_stream[i], cudaStreamNonBlocking));
+  for (int i = 0; i < 4; i++)
+    if (!h->yk_ev[i]) MATM_CUDA(h, cudaEventCreateWithFlags(&h->yk_ev[i], cudaEventDisableTiming));
+  const size_t smem = synth_f32_smem();
+  MATM_CUDA(h, cudaFuncSetAttribute(synth_eval_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // the scratch buffers are shared by every call on this handle: order this call after the previous one
+  if (h->yk_used) {
+    MATM_CUDA(h, cudaStreamWaitEvent(st, h->yk_ev[3], 0));
+  }
+  if (two) {
+    MATM_CUDA(h, cudaEventRecord(h->yk_ev[0], st));
+    MATM_CUDA(h, cudaStreamWaitEvent(h->yk_stream[0], h->yk_ev[0], 0));
+    MATM_CUDA(h, cudaStreamWaitEvent(h->yk_stream[1], h->yk_ev[0], 0));
+  }
+  for (int64_t c = 0; c < n_chunks; c++) {
+    const int64_t t0 = c * chunk, nt = min(chunk, n_tiles - t0);
+    cudaStream_t s = two ? h->yk_stream[c & 1] : st;
+    float* yk = h->yk_buf[two ? (c & 1) : 0];
+    loading_f32_kernel<<<(unsigned)(nt * n_kb), LD_THREADS, 0, s>>>(P, order, tile_m, t0, n_det, yk, apply_gain);
+    MATM_LAUNCHED(h);
+    synth_eval_f32_kernel<<<(unsigned)(nt * n_tt), F32_THREADS, smem, s>>>(P, order, t0, det0, n_det, yk, out, units);
+    MATM_LAUNCHED(h);
+  }
+  if (two) {
+    for (int i = 0; i < 2; i++) {
+      MATM_CUDA(h, cudaEventRecord(h->yk_ev[1 + i], h->yk_stream[i]));
+      MATM_CUDA(h, cudaStreamWaitEvent(st, h->yk_ev[1 + i], 0));
+    }
+  }
+  MATM_CUDA(h, cudaEventRecord(h->yk_ev[3], st));
+  h->yk_used = true;
+  return MATM_OK;
+}
+
 static int launch_synth(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, int units, int apply_gain,
                         cudaStream_t st) {
   const SynthParams& P = h->P;
@@ -291,25 +356,8 @@ static int launch_synth(matm_handle* h, int64_t det0, int64_t n_det, void* out_d
     size_t smem = synth_smem<double>(P.n_layers);
     MATM_CUDA(h, cudaFuncSetAttribute(synth_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     synth_kernel<double><<<(unsigned)blocks, SY_THREADS, smem, st>>>(P, det0, n_det, (double*)out_dev, units, apply_gain);
-  } else if (getenv("MATM_SYNTH_GENERIC") == nullptr) {
-    // production float kernel (matm_synth_f32.cuh)
-    const int n_ttiles = (P.n_t_atm - 1 + F32_KT - 1) / F32_KT;
-    const int64_t blocks = ((n_det + F32_DT - 1) / F32_DT) * n_ttiles;
-    if (blocks > INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize: too many tiles; split the detector range");
-    const int32_t* order = nullptr;
-    const uint8_t* tile_m = nullptr;
-    int rc = matm_detector_order(h, det0, n_det, &order, &tile_m);
-    if (rc) return rc;
-    size_t smem = synth_f32_smem(P.n_layers);
-    MATM_CUDA(h, cudaFuncSetAttribute(synth_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    synth_f32_kernel<<<(unsigned)blocks, F32_THREADS, smem, st>>>(P, order, tile_m, det0, n_det, (float*)out_dev, units, apply_gain);
   } else {
-    const int n_ttiles = (P.n_t_atm - 1 + Tile<float>::KT - 1) / Tile<float>::KT;
-    const int64_t blocks = ((n_det + DT - 1) / DT) * n_ttiles;
-    if (blocks > INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize: too many tiles; split the detector range");
-    size_t smem = synth_smem<float>(P.n_layers);
-    MATM_CUDA(h, cudaFuncSetAttribute(synth_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    synth_kernel<float><<<(unsigned)blocks, SY_THREADS, smem, st>>>(P, det0, n_det, (float*)out_dev, units, apply_gain);
+    return launch_synth_f32(h, det0, n_det, (float*)out_dev, units, apply_gain, st);
   }
   MATM_LAUNCHED(h);
   return MATM_OK;
@@ -339,6 +387,14 @@ extern "C" int matm_calibrate(matm_handle* h, int64_t det0, int64_t n_det, const
   else
     calibrate_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(h->P, det0, n_det, (const float*)in_dev, (float*)out_dev, to_units);
   MATM_LAUNCHED(h);
+  return MATM_OK;
+}
+
+extern "C" int matm_set_tuning(matm_handle* h, int chunk_mib, int overlap) {
+  MATM_CHECK_HANDLE(h);
+  if (chunk_mib < 1 || chunk_mib > 65536) MATM_FAIL_ARG(h, "matm_set_tuning: chunk_mib must be in [1, 65536]");
+  h->chunk_mib = chunk_mib;
+  h->overlap = overlap != 0;
   return MATM_OK;
 }
 

@@ -1,15 +1,17 @@
-// The production (float) instance of the fused synthesis kernel a6..a14, written for instruction count: the kernel is
-// issue- and data-pipe-bound, not HBM-bound (ncu: ~140 thread-instructions per output sample in the generic template,
-// ~37 here), so every per-output-sample operation is stripped to the minimum and done on two detectors at once with
-// the packed fma.rn.f32x2 / mul / add instructions of sm_100.
+// The production (float) path of the fused synthesis a6..a14, as TWO kernels per detector chunk, written for instruction
+// count (ncu: the one-kernel version was issue- and latency-bound at 35 thread-instructions per output sample, not
+// HBM-bound):
 //
-//   phase 1  loading [pW] at the window's knots; lane = focal-plane position (co-located detectors share the line of
-//            sight: tile multiplicity M), warps stride over knots, F32_G knots per thread                (per knot)
-//   phase 2  not-a-knot cubic spline second derivatives by the windowed Thomas sweep                     (per knot)
-//   phase 3  spline evaluation + pW -> K_RJ at the full-rate samples; thread = F32_S samples, loop over   (per sample)
-//            detector PAIRS: 2 LDS.128 + 4 packed FMAs for the spline; the calibration factor is
-//            rcp(Hc + Hs asin(sin el)) in packed arithmetic when the tile lies in one interval of the elevation
-//            grid, else the t = sqrt(1 - sin el) table of matm_setup.cu (no search, no divide).
+//   loading_f32_kernel   (per knot)    loading [pW] at the atmosphere-rate knots: lane = focal-plane position (co-located
+//                                      detectors share the line of sight: tile multiplicity M), F32_G knots per thread,
+//                                      8 bilinear gathers from the L2-resident layers, emission lookup, x Mueller x gain
+//                                      -> yk[tile][knot][32 slots] (an L2-sized scratch of the chunk, no halo, own occupancy)
+//   synth_eval_f32_kernel (per sample) window of yk -> shared memory; not-a-knot cubic spline second derivatives by the
+//                                      windowed Thomas sweep; evaluation + pW -> K_RJ at the full-rate samples: thread =
+//                                      F32_S samples, loop over detector PAIRS in packed f32x2 arithmetic.  The calibration
+//                                      factor is rcp of a QUADRATIC in the boresight elevation with per-(detector, tile)
+//                                      coefficients (every transcendental depends on time only through el_b), else the
+//                                      t = sqrt(1 - sin el) table of matm_setup.cu.
 #pragma once
 #include <type_traits>
 #include "matm_synth.cuh"
@@ -17,11 +19,9 @@
 #define F32_DT 32
 #define F32_THREADS 256
 #ifndef F32_KT
-// spline intervals per tile.  Both per-tile loops are quantised: phase 1 works in passes of 8 M F32_G knots over the
-// KT + 1 + 2 HALO knots of the window, phase 3 in iterations of 256 F32_S samples over the KT U samples of the tile
-// (U = full-rate samples per interval).  135 fills both at the C4 cadence (U = 22.6: 156 knots = 2.5 passes of 64,
-// 3056 samples = 3.98 iterations of 768) and keeps three CTAs per SM; any value is correct (-DF32_KT=... retunes).
-#define F32_KT 135
+// spline intervals per tile of the evaluation kernel: its window of F32_KT + 1 + 2 F32_HALO knots x 16 pairs x 16 bytes
+// plus the 38 KB of staging / records decide how many CTAs fit an SM (96: 70 KB, three CTAs); any value is correct.
+#define F32_KT 96
 #endif
 #ifndef F32_HALO
 #define F32_HALO 10  // extra knots each side; the error of the artificial boundary decays as (2 - sqrt 3)^HALO
@@ -33,10 +33,6 @@
 #define F32_NP (F32_DT / 2)  // detector pairs per tile
 #ifndef F32_KS
 #define F32_KS F32_NP  // float4 entries per knot row of ym4 (padding the rows by one entry was measured: no gain, 5.21 vs 5.09 ms)
-#endif
-#define F32_SPLN ((5 * F32_W + 3) & ~3)  // floats reserved for the spline system (keeps what follows 16-byte aligned)
-#ifndef F32_S
-#define F32_S 3  // full-rate samples per thread and iteration in phase 3 (4 spills at 80 registers)
 #endif
 #ifndef F32_G
 #define F32_G 4  // knots per thread and iteration in phase 1
@@ -80,19 +76,6 @@ __device__ __forceinline__ float fast_asin(float x) {
   p = fmaf(p, a, 1.5707963050f);
   const float r = fmaf(-fast_sqrt(fmaxf(1.0f - a, 0.0f)), p, 1.5707963268f);
   return copysignf(r, x);
-}
-
-// the same for two arguments in [0, 1] at once, given sq = sqrt(1 - x): pi/2 - sq P7(x), the polynomial in packed f32x2
-__device__ __forceinline__ float2 asin01_f32x2(float2 x, float2 sq) {
-  float2 p = f2(0.0012624911f, 0.0012624911f);  // -P7: the subtraction becomes the last FMA
-  p = __ffma2_rn(p, x, f2(-0.0066700901f, -0.0066700901f));
-  p = __ffma2_rn(p, x, f2(0.0170881256f, 0.0170881256f));
-  p = __ffma2_rn(p, x, f2(-0.0308918810f, -0.0308918810f));
-  p = __ffma2_rn(p, x, f2(0.0501743046f, 0.0501743046f));
-  p = __ffma2_rn(p, x, f2(-0.0889789874f, -0.0889789874f));
-  p = __ffma2_rn(p, x, f2(0.2145988016f, 0.2145988016f));
-  p = __ffma2_rn(p, x, f2(-1.5707963050f, -1.5707963050f));
-  return __ffma2_rn(sq, p, f2(1.5707963268f, 1.5707963268f));
 }
 
 // The calibration factor in a special bin of the table (calq_kind != 0): a bin holding one grid point of the elevation
@@ -161,191 +144,171 @@ __device__ __forceinline__ float emission_blend_f32(const SynthParams& P, int ba
   return fmaf(wp, b - a, a);
 }
 
-// Phase 1 of the fused kernel: loading [pW] at the window's knots, for a tile whose detectors come in groups of M
-// co-located ones (dichroic pixels, both polarisations: same offsets, hence the same line of sight through every layer).
-// Each thread works on F32_G knots at once: F32_G independent gather chains per layer keep 4 F32_G loads in flight (the
-// layers live in L2; a dependent chain per knot leaves the SM waiting on that latency), and the per-layer constants are
-// fetched once per group.
+
+// ---------------------------------------------------------------------------------------------------------
+// Kernel A: loading [pW] at the atmosphere-rate knots (a6 + a7 + a9 + a11 + a12 x Mueller, a13 gain folded in).
+// One CTA = one tile of 32 processing-order slots x LD_KA knots.  Detectors that share a position (the bands of a
+// dichroic pixel, both polarisations) share the line of sight through every layer: for a tile whose slots come in aligned
+// groups of M co-located detectors, lanes [0, 32 / M) of a warp are the tile's positions, the other lanes take further
+// knots (M "virtual warps" per warp), and each lane finishes M detectors (band table, Mueller, gain).  Each thread works
+// on F32_G knots at once: F32_G independent gather chains per layer keep 4 F32_G loads in flight (the layers live in L2).
+// ---------------------------------------------------------------------------------------------------------
+#define LD_THREADS 256
+#ifndef LD_KA
+#define LD_KA 128  // knots per CTA: 1 (M = 4), 2 (M = 2) or 4 (M = 1) passes of F32_G knots per thread
+#endif
+#ifndef LD_MINB
+#define LD_MINB 3
+#endif
+
 template <int M>
-__device__ __forceinline__ void phase1_f32(const SynthParams& P, const int32_t* __restrict__ order, int64_t dbase, int nd, int wa,
-                                           int Wn, int n_layers, const Knot<float>* knots, const LayerKnot<float>* lk,
-                                           const LayerF* ls, float* ymf, const float* dc_gain, const int* dc_band,
-                                           const float* dc_mu, int lane, int warp) {
-  {
-    // M detectors share every line of sight: lanes [0, 32 / M) of a warp are the tile's positions, the other lanes take
-    // further knots (M "virtual warps" per warp), and each lane finishes M detectors (band tables, Mueller, gain)
-    constexpr int PL = 32 / M;
-    const int slot0 = (lane % PL) * M, sub = lane / PL;
-    const int64_t d = order[dbase + min(slot0, nd - 1)];  // idle lanes of a partial tile shadow the last detector
-    const double* da = P.det_atm + 4 * d;
-    const float u = (float)da[0], Y = (float)da[1], wm1 = (float)da[2];
-    const float pwv0 = (float)P.pwv0;
-    int ip = 0, ie = 0;
-    constexpr int NW = (F32_THREADS / 32) * M;
-    // one pass = G knots per thread, NW * G knots per CTA.  Full passes use F32_G; what is left at the end of the window
-    // takes the smallest G that covers it, so a window of 148 knots costs 2.5 passes of 64 (M = 2) instead of 3.
-    auto pass = [&](auto gtag, const int kb) {
-      constexpr int G = decltype(gtag)::value;
-      float dppx[G], dppy[G], sinel[G], acc[G];
-      int kk[G];
-      bool bad = false;
+__device__ __forceinline__ void loading_tile_f32(const SynthParams& P, const int32_t* __restrict__ order, int64_t dbase, int nd,
+                                                 int ka, int Wn, int n_layers, const LayerF* ls, const float* dc_gain,
+                                                 const int* dc_band, const float* dc_mu, float* __restrict__ yrow, int lane,
+                                                 int warp) {
+  constexpr int PL = 32 / M;
+  const int slot0 = (lane % PL) * M, sub = lane / PL;
+  const int64_t d = order[dbase + min(slot0, nd - 1)];  // idle lanes of a partial tile shadow the last detector
+  const double* da = P.det_atm + 4 * d;
+  const float u = (float)da[0], Y = (float)da[1], wm1 = (float)da[2];
+  const float pwv0 = (float)P.pwv0;
+  const LayerKnot<float>* __restrict__ lk = reinterpret_cast<const LayerKnot<float>*>(P.lk_tab);
+  const int n = P.n_t_atm;
+  int ip = 0, ie = 0;
+  constexpr int NW = (LD_THREADS / 32) * M;
+  // one pass = G knots per thread, NW * G knots per CTA.  Full passes use F32_G; what is left at the end of the block
+  // takes the smallest G that covers it.
+  auto pass = [&](auto gtag, const int kb) {
+    constexpr int G = decltype(gtag)::value;
+    float dppx[G], dppy[G], sinel[G], acc[G];
+    int kk[G];
+    bool bad = false;
+#pragma unroll
+    for (int q = 0; q < G; q++) {
+      kk[q] = ka + min(kb + q * NW, Wn - 1);  // a short last group repeats the last knot (same value, same slot)
+      const float4 kc = __ldg(P.knot_f + kk[q]);  // ce, se, ca, sa
+      // direction of the detector minus direction of the boresight, horizon frame (coords/transforms.py:10-29)
+      const float dX = u * kc.x - wm1 * kc.y;
+      const float dZ = u * kc.y + wm1 * kc.x;
+      const float dNx = dX * kc.z - Y * kc.w;
+      const float dNy = dX * kc.w + Y * kc.z;
+      const float Nbx = -kc.y * kc.z, Nby = -kc.y * kc.w, Nbz = kc.x;
+      const float Nz = Nbz + dZ;  // = sin(el) of the detector
+      const float inv = fast_rcp(Nbz * Nz);
+      dppx[q] = (dNx * Nbz - Nbx * dZ) * inv;  // pp_d - pp_b (coordinates.py:333-349)
+      dppy[q] = (dNy * Nbz - Nby * dZ) * inv;
+      sinel[q] = Nz;
+      acc[q] = 0.f;
+      bad = bad || !(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]);
+    }
+    unsigned badmask = 0;
+    for (int l = 0; l < n_layers; l++) {
+      const float4 Dm = *reinterpret_cast<const float4*>(&ls[l].D0);
+      const int4 Ln = *reinterpret_cast<const int4*>(&ls[l].rms);
+      const float* data = ls[l].data;
+      float wx[G], wy[G];
+      const float* v[G];
 #pragma unroll
       for (int q = 0; q < G; q++) {
-        kk[q] = min(kb + q * NW, Wn - 1);  // a short last group repeats the last knot (same value, same slot)
-        const Knot<float> kc = knots[kk[q]];
-        // direction of the detector minus direction of the boresight, horizon frame (coords/transforms.py:10-29)
-        const float dX = u * kc.ce - wm1 * kc.se;
-        const float dZ = u * kc.se + wm1 * kc.ce;
-        const float dNx = dX * kc.ca - Y * kc.sa;
-        const float dNy = dX * kc.sa + Y * kc.ca;
-        const float Nbx = -kc.se * kc.ca, Nby = -kc.se * kc.sa, Nbz = kc.ce;
-        const float Nz = Nbz + dZ;  // = sin(el) of the detector
-        const float inv = fast_rcp(Nbz * Nz);
-        dppx[q] = (dNx * Nbz - Nbx * dZ) * inv;  // pp_d - pp_b (coordinates.py:333-349)
-        dppy[q] = (dNy * Nbz - Nby * dZ) * inv;
-        sinel[q] = Nz;
-        acc[q] = 0.f;
-        bad = bad || !(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]);
-      }
-      unsigned badmask = 0;
-      for (int l = 0; l < n_layers; l++) {
-        const float4 Dm = *reinterpret_cast<const float4*>(&ls[l].D0);
-        const int4 Ln = *reinterpret_cast<const int4*>(&ls[l].rms);
-        const float* data = ls[l].data;
-        float wx[G], wy[G];
-        const float* v[G];
-#pragma unroll
-        for (int q = 0; q < G; q++) {
-          const LayerKnot<float> b = lk[l * F32_W + kk[q]];
-          const float fx = fmaf(Dm.x, dppx[q], fmaf(Dm.y, dppy[q], b.fx));
-          const float fy = fmaf(Dm.z, dppx[q], fmaf(Dm.w, dppy[q], b.fy));
-          const float flx = floorf(fx), fly = floorf(fy);
-          int ix = b.ix + (int)flx, iy = b.iy + (int)fly;
-          wx[q] = fx - flx;
-          wy[q] = fy - fly;
-          if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
-            // rare: exactly on the last grid line is inside (RGI clips the index to n - 2); anything else is outside
-            if (ix == Ln.y && wx[q] == 0.f) {
-              ix--;
-              wx[q] = 1.f;
-            }
-            if (iy == Ln.z && wy[q] == 0.f) {
-              iy--;
-              wy[q] = 1.f;
-            }
-            if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
-              record_out_of_grid(P.flags, l, d, wa + kk[q]);  // atmosphere.py:368-369
-              badmask |= 1u << q;
-              ix = iy = 0;
-            }
+        const int4 braw = __ldg(reinterpret_cast<const int4*>(lk + (size_t)l * n + kk[q]));
+        const float bfx = __int_as_float(braw.z), bfy = __int_as_float(braw.w);
+        const float fx = fmaf(Dm.x, dppx[q], fmaf(Dm.y, dppy[q], bfx));
+        const float fy = fmaf(Dm.z, dppx[q], fmaf(Dm.w, dppy[q], bfy));
+        const float flx = floorf(fx), fly = floorf(fy);
+        int ix = braw.x + (int)flx, iy = braw.y + (int)fly;
+        wx[q] = fx - flx;
+        wy[q] = fy - fly;
+        if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
+          // rare: exactly on the last grid line is inside (RGI clips the index to n - 2); anything else is outside
+          if (ix == Ln.y && wx[q] == 0.f) {
+            ix--;
+            wx[q] = 1.f;
           }
-          v[q] = data + (ix * Ln.w + iy);
+          if (iy == Ln.z && wy[q] == 0.f) {
+            iy--;
+            wy[q] = 1.f;
+          }
+          if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
+            record_out_of_grid(P.flags, l, d, kk[q]);  // atmosphere.py:368-369
+            badmask |= 1u << q;
+            ix = iy = 0;
+          }
         }
-        float v00[G], v01[G], v10[G], v11[G];
+        v[q] = data + (ix * Ln.w + iy);
+      }
+      float v00[G], v01[G], v10[G], v11[G];
 #pragma unroll
-        for (int q = 0; q < G; q++) {
-          v00[q] = __ldg(v[q]);
-          v01[q] = __ldg(v[q] + 1);
-          v10[q] = __ldg(v[q] + Ln.w);
-          v11[q] = __ldg(v[q] + Ln.w + 1);
-        }
-#pragma unroll
-        for (int q = 0; q < G; q++) {
-          const float a = fmaf(wy[q], v01[q] - v00[q], v00[q]), bb = fmaf(wy[q], v11[q] - v10[q], v10[q]);
-          acc[q] = fmaf(__int_as_float(Ln.x), fmaf(wx[q], bb - a, a), acc[q]);
-        }
+      for (int q = 0; q < G; q++) {
+        v00[q] = __ldg(v[q]);
+        v01[q] = __ldg(v[q] + 1);
+        v10[q] = __ldg(v[q] + Ln.w);
+        v11[q] = __ldg(v[q] + Ln.w + 1);
       }
 #pragma unroll
       for (int q = 0; q < G; q++) {
-        if (bad || ((badmask >> q) & 1)) {
-          if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, wa + kk[q]);
-          if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
-        }
-        float wp, we;
-        const bool ok = emission_cell_f32(P, pwv0 + acc[q], sinel[q], ip, ie, wp, we);
+        const float a = fmaf(wy[q], v01[q] - v00[q], v00[q]), bb = fmaf(wy[q], v11[q] - v10[q], v10[q]);
+        acc[q] = fmaf(__int_as_float(Ln.x), fmaf(wx[q], bb - a, a), acc[q]);
+      }
+    }
 #pragma unroll
-        for (int j = 0; j < M; j++) {
-          const int sl = slot0 + j;
-          // times Mueller [0,0]; the spline being linear in the data, the detector gain goes in here too
-          const float y = ok ? emission_blend_f32(P, dc_band[sl], ip, ie, wp, we) * dc_mu[sl] * dc_gain[sl] : r_nan<float>();
-          if (kb + q * NW < Wn) ymf[(kk[q] * F32_KS + (sl >> 1)) * 4 + (sl & 1)] = y;
-        }
+    for (int q = 0; q < G; q++) {
+      if (bad || ((badmask >> q) & 1)) {
+        if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, kk[q]);
+        if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
       }
-    };
-    const int vw = warp * M + sub;
-    for (int base = 0; base < Wn;) {
-      const int rem = Wn - base;
-      if (rem > (F32_G / 2) * NW) {
-        pass(std::integral_constant<int, F32_G>{}, base + vw);
-        base += F32_G * NW;
-      } else if (rem > NW) {
-        pass(std::integral_constant<int, F32_G / 2>{}, base + vw);
-        base += (F32_G / 2) * NW;
-      } else {
-        pass(std::integral_constant<int, 1>{}, base + vw);
-        base += NW;
+      float wp, we;
+      const bool ok = emission_cell_f32(P, pwv0 + acc[q], sinel[q], ip, ie, wp, we);
+      float y[M];
+#pragma unroll
+      for (int j = 0; j < M; j++) {
+        const int sl = slot0 + j;
+        // times Mueller [0,0]; the spline being linear in the data, the detector gain goes in here too
+        y[j] = ok ? emission_blend_f32(P, dc_band[sl], ip, ie, wp, we) * dc_mu[sl] * dc_gain[sl] : r_nan<float>();
+        if (sl >= nd) y[j] = 0.f;  // unused slots of a partial tile
       }
+      if (kb + q * NW < Wn) {
+        float* o = yrow + (size_t)kk[q] * F32_DT + slot0;
+        if constexpr (M == 1) *o = y[0];
+        if constexpr (M == 2) *reinterpret_cast<float2*>(o) = make_float2(y[0], y[1]);
+        if constexpr (M == 4) *reinterpret_cast<float4*>(o) = make_float4(y[0], y[1], y[2], y[3]);
+      }
+    }
+  };
+  const int vw = warp * M + sub;
+  for (int base = 0; base < Wn;) {
+    const int rem = Wn - base;
+    if (rem > (F32_G / 2) * NW) {
+      pass(std::integral_constant<int, F32_G>{}, base + vw);
+      base += F32_G * NW;
+    } else if (rem > NW) {
+      pass(std::integral_constant<int, F32_G / 2>{}, base + vw);
+      base += (F32_G / 2) * NW;
+    } else {
+      pass(std::integral_constant<int, 1>{}, base + vw);
+      base += NW;
     }
   }
 }
 
-__global__ void __launch_bounds__(F32_THREADS, F32_MINB)
-    synth_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order,
-                     const uint8_t* __restrict__ tile_m, int64_t det0, int64_t n_det,
-                     float* __restrict__ out, int units, int apply_gain) {
-  extern __shared__ __align__(16) unsigned char dyn[];
-  float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_d0, y_d1, m_d0, m_d1}
-  float* ymf = reinterpret_cast<float*>(dyn);
-  float4* splq = ym4 + F32_W * F32_KS;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
-  float* h26 = reinterpret_cast<float*>(splq + F32_W);               // [W] h_k^2 / 6
-  Knot<float>* knots = reinterpret_cast<Knot<float>*>(reinterpret_cast<float*>(splq) + F32_SPLN);
-  LayerKnot<float>* lk = reinterpret_cast<LayerKnot<float>*>(knots + F32_W);  // [n_layers][W]
+// yk: [n_tiles of this launch][n_t_atm][32] float; tile0 = first tile (of the requested detector range) of this launch
+__global__ void __launch_bounds__(LD_THREADS, LD_MINB)
+    loading_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order,
+                       const uint8_t* __restrict__ tile_m, int64_t tile0, int64_t n_det, float* __restrict__ yk,
+                       int apply_gain) {
   __shared__ __align__(16) LayerF ls[MATM_MAX_LAYERS];
-  __shared__ float4 dc_uw[F32_NP];  // {u_d0, u_d1, w_d0, w_d1} of the rolled offsets
-  __shared__ int2 dc_tab[F32_NP];   // calibration-table base of each detector's band, minus the rounding magic
   __shared__ float dc_gain[F32_DT];
   __shared__ int dc_band[F32_DT];
   __shared__ float dc_mu[F32_DT];
-  __shared__ __align__(16) long long dc_row[F32_DT];  // byte offset of each detector's output row
-  __shared__ float4 dc_cal[F32_NP];  // {Hc_d0, Hc_d1, Hs_d0, Hs_d1}: the line H(el) of the tile's elevation interval (s_cal_ie >= 0)
-  __shared__ int s_cal_ie;
-
   const int n = P.n_t_atm;
-  const int n_int = n - 1;
-  const int n_layers = P.n_layers;
-  const int n_ttiles = (n_int + F32_KT - 1) / F32_KT;
-  const int64_t dtile = blockIdx.x / n_ttiles;
-  const int ttile = blockIdx.x % n_ttiles;
-  const int k0 = ttile * F32_KT, k1 = min(k0 + F32_KT, n_int);
-  const int wa = max(0, k0 - F32_HALO), wb = min(n - 1, k1 + F32_HALO);
-  const int Wn = wb - wa + 1;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n_kb = (n + LD_KA - 1) / LD_KA;
+  const int64_t tl = blockIdx.x / n_kb;  // tile within this launch
+  const int kb = blockIdx.x % n_kb;
+  const int ka = kb * LD_KA, Wn = min(LD_KA, n - ka);
+  const int64_t dtile = tile0 + tl;
   const int64_t dbase = dtile * F32_DT;
   const int nd = (int)min((int64_t)F32_DT, n_det - dbase);
-  constexpr int MAGIC_BITS = 0x4B400000;  // bits of 1.5 * 2^23
-
-  // ---- stage the window: knots, per-layer boresight cells, per-layer constants, spline system, detector constants ----
-  for (int k = tid; k < Wn; k += F32_THREADS) {
-    const double* b = P.bore_atm + 4 * (size_t)(wa + k);
-    Knot<float> o;
-    o.ce = (float)b[0];
-    o.se = (float)b[1];
-    o.ca = (float)b[2];
-    o.sa = (float)b[3];
-    knots[k] = o;
-  }
-  for (int e = tid; e < n_layers * Wn; e += F32_THREADS) {
-    const int l = e / Wn, k = e % Wn;
-    const double* b = P.layers[l].base + 2 * (size_t)(wa + k);
-    const double cx = b[0], cy = b[1];
-    const double flx = fmin(fmax(floor(cx), -1.0e9), 1.0e9), fly = fmin(fmax(floor(cy), -1.0e9), 1.0e9);
-    LayerKnot<float> o;
-    o.ix = (int)flx;
-    o.iy = (int)fly;
-    o.fx = (float)(cx - flx);
-    o.fy = (float)(cy - fly);
-    lk[l * F32_W + k] = o;
-  }
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n_layers = P.n_layers;
   if (tid < n_layers) {
     const LayerDev& L = P.layers[tid];
     LayerF o;
@@ -361,16 +324,12 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     o.pad[0] = o.pad[1] = 0;
     ls[tid] = o;
   }
-  if (tid < F32_DT) {
-    const int dd = tid;
-    float u = 0.f, w = 1.f, g = 0.f, mu = 0.f;
+  if (tid >= 32 && tid < 32 + F32_DT) {
+    const int dd = tid - 32;
+    float g = 0.f, mu = 0.f;
     int band = 0;
-    long long row = 0;
     if (dd < nd) {
-      const int64_t d = order[dbase + dd];  // absolute detector index of this slot
-      row = (d - det0) * P.n_t * (long long)sizeof(float);
-      u = (float)P.det_full[2 * d];
-      w = (float)P.det_full[2 * d + 1];
+      const int64_t d = order[dbase + dd];
       g = apply_gain ? (float)P.gain[d] : 1.f;
       band = P.band_index[d];
       mu = (float)P.mueller00[d];
@@ -378,68 +337,165 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     dc_mu[dd] = mu;
     dc_gain[dd] = g;
     dc_band[dd] = band;
+  }
+  __syncthreads();
+  float* yrow = yk + (size_t)tl * n * F32_DT;
+  const int tm = nd == F32_DT ? tile_m[dtile] : 1;
+  if (tm == 4)
+    loading_tile_f32<4>(P, order, dbase, nd, ka, Wn, n_layers, ls, dc_gain, dc_band, dc_mu, yrow, lane, warp);
+  else if (tm == 2)
+    loading_tile_f32<2>(P, order, dbase, nd, ka, Wn, n_layers, ls, dc_gain, dc_band, dc_mu, yrow, lane, warp);
+  else
+    loading_tile_f32<1>(P, order, dbase, nd, ka, Wn, n_layers, ls, dc_gain, dc_band, dc_mu, yrow, lane, warp);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Kernel B: spline + evaluation + calibration.  One CTA = one tile of 32 slots x F32_KT spline intervals (+ F32_HALO knots
+// of yk on either side for the windowed Thomas sweep).
+//
+// Evaluation (phase 3) is organised for instruction count and for the store path:
+//   * lane = detector PAIR (slots p and p + 16) x half-warp; every arithmetic instruction is a packed f32x2 over the pair.
+//     The spline data of the current interval {y_k, y_k+1 - y_k, M_k, M_k+1} live in registers and are reloaded only when
+//     the interval changes; what depends on the sample only -- the cubic weights a1, a2, a3 (float4 table written once per
+//     scan by sample_weights_kernel) and x = el_b(t) - e_mid -- is one 16-byte record per sample, staged in shared memory
+//     per 128-sample sub-chunk and read as a broadcast LDS.128;
+//   * a thread finishes 4 consecutive samples of its two detectors and puts them into a [32 rows][128 samples] staging
+//     buffer with two conflict-free STS.128; the rows leave through the TMA: one cp.async.bulk.global.shared::cta of up to
+//     512 bytes per row and sub-chunk (L2 evict-first), double-buffered, one CTA barrier per sub-chunk.  No per-sample
+//     address arithmetic, no per-thread global store.
+// ---------------------------------------------------------------------------------------------------------
+#define F32_SUB 128                 // samples per sub-chunk (= row segment handed to the TMA)
+#define F32_RS (F32_SUB + 4)        // staging row stride in floats: 16-byte aligned rows, r * RS mod 32 = 4 r
+__device__ __forceinline__ uint32_t f32_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__global__ void __launch_bounds__(F32_THREADS, F32_MINB)
+    synth_eval_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order, int64_t tile0,
+                          int64_t det0, int64_t n_det, const float* __restrict__ yk, float* __restrict__ out, int units) {
+  extern __shared__ __align__(128) unsigned char dyn[];
+  float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_p, y_p+16, m_p, m_p+16}
+  float* ymf = reinterpret_cast<float*>(dyn);
+  float4* splq = ym4 + F32_W * F32_KS;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
+  float* stage = reinterpret_cast<float*>(splq + F32_W);             // [2][32][F32_RS]
+  float4* rec = reinterpret_cast<float4*>(stage + 2 * F32_DT * F32_RS);  // [2][F32_SUB] {a1, a2, a3, x}
+  int* rli = reinterpret_cast<int*>(rec + 2 * F32_SUB);              // [2][F32_SUB] local interval of the sample
+  float2* rcs = reinterpret_cast<float2*>(rli + 2 * F32_SUB);        // [2][F32_SUB] {cos, sin}(el_b - pi/2)  (MODE 1 only)
+  __shared__ float dc_u[F32_DT], dc_w[F32_DT];  // rolled offsets: sin el_d = u sin(e) + w cos(e)
+  __shared__ int dc_tab[F32_DT];                // calibration-table base of each detector's band, minus the rounding magic
+  __shared__ int dc_band[F32_DT];
+  __shared__ long long dc_row[F32_DT];          // element offset of each detector's output row
+  __shared__ float dc_p0[F32_DT], dc_p1[F32_DT], dc_p2[F32_DT];  // 1 / factor = P0 + x (P1 + x P2), x = el_b(t) - e_mid
+  __shared__ int s_cal_ie;
+  __shared__ double s_emid;
+
+  const int n = P.n_t_atm;
+  const int n_int = n - 1;
+  const int n_ttiles = (n_int + F32_KT - 1) / F32_KT;
+  const int64_t tl = blockIdx.x / n_ttiles;
+  const int64_t dtile = tile0 + tl;
+  const int ttile = blockIdx.x % n_ttiles;
+  const int k0 = ttile * F32_KT, k1 = min(k0 + F32_KT, n_int);
+  const int wa = max(0, k0 - F32_HALO), wb = min(n - 1, k1 + F32_HALO);
+  const int Wn = wb - wa + 1;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t dbase = dtile * F32_DT;
+  const int nd = (int)min((int64_t)F32_DT, n_det - dbase);
+  constexpr int MAGIC_BITS = 0x4B400000;  // bits of 1.5 * 2^23
+  const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
+  if (j0 >= j1) return;  // a time tile that owns no full-rate sample (sample spacing > F32_KT knots)
+  const bool krj = units == MATM_UNITS_KRJ;
+
+  // ---- stage the window: loading at the knots (kernel A's output), spline system, detector constants ----
+  {
+    const float* __restrict__ src = yk + ((size_t)tl * n + wa) * F32_DT;
+    for (int e = tid; e < Wn * F32_DT; e += F32_THREADS) {
+      const int k = e >> 5, sl = e & 31;
+      ymf[(k * F32_KS + (sl & 15)) * 4 + (sl >> 4)] = __ldcs(src + e);  // read once (plus the halo): streaming
+    }
+  }
+  if (tid < F32_DT) {
+    const int dd = tid;
+    float u = 0.f, w = 1.f;
+    int band = 0;
+    long long row = 0;
+    if (dd < nd) {
+      const int64_t d = order[dbase + dd];  // absolute detector index of this slot
+      row = (d - det0) * P.n_t;
+      u = (float)P.det_full[2 * d];
+      w = (float)P.det_full[2 * d + 1];
+      band = P.band_index[d];
+    }
+    dc_band[dd] = band;
     dc_row[dd] = row;
-    float* uw = reinterpret_cast<float*>(dc_uw);
-    uw[(dd >> 1) * 4 + (dd & 1)] = u;
-    uw[(dd >> 1) * 4 + 2 + (dd & 1)] = w;
-    reinterpret_cast<int*>(dc_tab)[dd] = band * P.calq_n - MAGIC_BITS;
+    dc_u[dd] = u;
+    dc_w[dd] = w;
+    dc_tab[dd] = band * P.calq_n - MAGIC_BITS;
   }
   if (warp == F32_THREADS / 32 - 1) {
-    // a14 without a table when the whole tile stays inside ONE interval of the elevation grid (the usual case: the grid
-    // steps are degrees wide): sin(el) of any detector at any sample of the window lies within the boresight's range at
-    // the knots, widened by the largest detector offset and by twice the largest knot-to-knot change (motion between knots)
-    float lo = 2.f, hi = -2.f, dmax = 0.f;
-    for (int k = lane; k < Wn; k += 32) {
-      const float c = (float)P.bore_atm[4 * (size_t)(wa + k)];
-      const float cn = (float)P.bore_atm[4 * (size_t)(wa + min(k + 1, Wn - 1))];
-      lo = fminf(lo, c);
-      hi = fmaxf(hi, c);
-      dmax = fmaxf(dmax, fabsf(cn - c));
+    // a14 without a table or a transcendental per sample when (1) every detector stays inside ONE interval of the elevation
+    // grid over the tile's full-rate samples (the usual case: the grid steps are degrees wide), so that H(el) = Hc + Hs el,
+    // and (2) the boresight elevation varies little enough over the tile for the quadratic expansion of el_d(el_b) about
+    // the tile's mid elevation to be exact to 5e-8 rad.  The range is taken over the FULL-RATE samples of the tile
+    // (el_rng), not the knots: turnarounds between knots and the extrapolated tail are covered.  All of it is a property
+    // of the time tile and of the whole focal plane (det_rmax), not of the shard: shards stay bit-identical.
+    double lo = INFINITY, hi = -INFINITY;
+    for (int k = k0 + lane; k < k1; k += 32) {
+      lo = fmin(lo, P.el_rng[2 * k]);
+      hi = fmax(hi, P.el_rng[2 * k + 1]);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-      lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-      hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-      dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+      lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+      hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
     }
     if (lane == 0) {
-      const float m = P.det_rmax_f + 2.f * dmax + 1e-6f;
-      lo -= m;
-      hi += m;
       int ie = -1;
-      if ((P.table_ok & 2) && units == MATM_UNITS_KRJ && lo == lo && hi == hi) {
+      const double emid = 0.5 * (lo + hi), xmax = 0.5 * (hi - lo), r = P.det_rmax * (1.0 + 1e-6) + 1e-7;
+      if ((P.table_ok & 2) && krj && lo == lo && hi == hi && hi + r < 1.5607963 /* pi/2 - 0.01 */ && lo - r > -1.5607963) {
+        const float slo = (float)sin(lo - r) - 2e-7f, shi = (float)sin(hi + r) + 2e-7f;
         const float* __restrict__ sing = reinterpret_cast<const float*>(P.sinel_R);
         for (int e = 0; e + 1 < P.nel; e++)
-          if (__ldg(sing + e) < lo && hi <= __ldg(sing + e + 1)) ie = e;
+          if (__ldg(sing + e) < slo && shi <= __ldg(sing + e + 1)) ie = e;
+        // remainder of the quadratic: |d^3 delta / de^3| x^3 / 6 with delta = el_b - beta - el_d ~ eps tan(theta),
+        // eps <= r^2 / 2: eps sec^2 (2 sec^2 + 4 tan^2) at the largest |elevation| a detector reaches
+        const double em = fmax(fabs(lo - r), fabs(hi + r)), c = cos(em), t = tan(em), s2 = 1.0 / (c * c);
+        const double rem = 0.5 * r * r * s2 * (2.0 * s2 + 4.0 * t * t) * xmax * xmax * xmax / 6.0;
+        if (!(rem <= 5e-8)) ie = -1;
       }
       s_cal_ie = ie;
+      s_emid = emid;
     }
   }
   for (int k = tid; k < Wn; k += F32_THREADS) {
     const double* sp = P.spl + 5 * (size_t)(wa + k);
     splq[k] = make_float4((float)sp[0], (float)sp[2], (float)sp[3], (float)sp[4]);
-    h26[k] = (float)sp[1];
   }
   __syncthreads();
-  if (tid < F32_DT && s_cal_ie >= 0) {
-    const int ho = dc_band[tid] * (P.nel - 1) + s_cal_ie;
-    float* cal = reinterpret_cast<float*>(dc_cal);
-    cal[(tid >> 1) * 4 + (tid & 1)] = __ldg(reinterpret_cast<const float*>(P.Hc_R) + ho);
-    cal[(tid >> 1) * 4 + 2 + (tid & 1)] = __ldg(reinterpret_cast<const float*>(P.Hs_R) + ho);
+  if (tid < F32_DT) {
+    // el_d(e) = asin(rho sin(e - beta)) = theta - delta(e), theta = e - beta, rho = 1 - eps; with c = cos el_d:
+    //   delta = asin(sin(theta) eps (2 - eps) / (c + rho cos theta))          (no cancellation; asin x = x to 1e-9)
+    //   delta' = 1 - f',  f' = rho cos(theta) / c,  1 - f' = eps (2 - eps) / ((c + rho cos theta) c)
+    //   delta'' = -f'' = tan(el_d) (1 - f') (1 + f')
+    // H(el_d(e_mid + x)) = Hc + Hs (theta_mid - delta) + Hs (1 - delta') x - Hs delta''/2 x^2 + O(x^3)
+    float p0 = 1.f, p1 = 0.f, p2 = 0.f;
+    if (tid < nd && s_cal_ie >= 0) {
+      const int64_t d = order[dbase + tid];
+      const int ho = dc_band[tid] * (P.nel - 1) + s_cal_ie;
+      const double hc = (double)__ldg(reinterpret_cast<const float*>(P.Hc_R) + ho), hs = (double)__ldg(reinterpret_cast<const float*>(P.Hs_R) + ho);
+      const double beta = P.det_cal[2 * d], eps = P.det_cal[2 * d + 1];
+      const double th = s_emid - beta, rho = 1.0 - eps;
+      double st, ct;
+      sincos(th, &st, &ct);
+      const double sf = rho * st, c = sqrt(fmax(1.0 - sf * sf, 1e-30));
+      const double g = eps * (2.0 - eps) / (c + rho * ct);
+      const double delta = st * g, d1 = g / c, fp = 1.0 - d1, d2 = (sf / c) * d1 * (1.0 + fp);
+      p0 = (float)(hc + hs * (th - delta));
+      p1 = (float)(hs * (1.0 - d1));
+      p2 = (float)(-0.5 * hs * d2);
+    }
+    dc_p0[tid] = p0;
+    dc_p1[tid] = p1;
+    dc_p2[tid] = p2;
   }
-
-  // ---- phase 1: loading [pW] at the window's knots (phase1_f32) ----
-  {
-    const int tm = nd == F32_DT ? tile_m[dtile] : 1;
-    if (tm == 4)
-      phase1_f32<4>(P, order, dbase, nd, wa, Wn, n_layers, knots, lk, ls, ymf, dc_gain, dc_band, dc_mu, lane, warp);
-    else if (tm == 2)
-      phase1_f32<2>(P, order, dbase, nd, wa, Wn, n_layers, knots, lk, ls, ymf, dc_gain, dc_band, dc_mu, lane, warp);
-    else
-      phase1_f32<1>(P, order, dbase, nd, wa, Wn, n_layers, knots, lk, ls, ymf, dc_gain, dc_band, dc_mu, lane, warp);
-  }
-  __syncthreads();
-
   // ---- phase 2: second derivatives M_k of the not-a-knot cubic spline through the window's knots; lane = detector.
   // Rows of the global tridiagonal system, swept with the global elimination factors.  At a true end of the series the
   // sweep starts / ends exactly; at an artificial end it starts from the locally-constant guess M = d / (a + b + c),
@@ -447,7 +503,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   // sweeps its own segment of rows plus F32_HALO rows of run-in on either side, so the serial chain is ~40 rows instead
   // of ~300 and no warp idles at the barrier for long.
   {
-    float* row = ymf + (lane >> 1) * 4 + (lane & 1);
+    float* row = ymf + (lane & 15) * 4 + (lane >> 4);
     constexpr int RS = F32_KS * 4;  // stride between knots, in floats
     constexpr int NW = F32_THREADS / 32;
     const int lo = 1, hi = Wn - 2, nrows = hi - lo + 1;
@@ -519,132 +575,148 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   }
   __syncthreads();
 
-  // ---- phase 3: evaluate at the full-rate samples of the tile ----
-  // thread = F32_S samples (j, j + 256, ...), loop over detector PAIRS; the per-pair constants (offsets, table base,
-  // output rows) are fetched once per F32_S samples: the kernel is bound by L1 wavefronts, not by arithmetic.
-  const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
-  const double t_atm0 = P.t_atm0, inv_ts = 1.0 / P.timestep;
-  const float inv_ts_f = (float)inv_ts;
-  const bool krj = units == MATM_UNITS_KRJ;
-  const int npairs = nd >> 1;
+  // ---- phase 3: evaluate at the full-rate samples of the tile (see the header of this kernel) ----
+  const int p = lane & 15, hw = lane >> 4;
+  const int mode = !krj ? 0 : (s_cal_ie >= 0 ? 2 : 1);
+  const double emid = s_emid;
+  const int64_t J0 = j0 & ~(int64_t)(F32_SUB - 1);
+  const int n_sub = (int)((j1 - J0 + F32_SUB - 1) / F32_SUB);
   const float2* __restrict__ calq = P.calq;
-  const float2 scale2 = f2(MATM_CAL_SCALE, MATM_CAL_SCALE), magic2 = f2(12582912.f, 12582912.f);
-  // a14 comes in three flavours, chosen per tile (the choice depends on the time window and on the whole focal plane, not
-  // on the detector shard, so shards stay bit-identical): MODE 0 no calibration (pW); MODE 1 the table in t; MODE 2 the
-  // whole tile lies in one interval of the elevation grid, H(el) = Hc + Hs el with el = asin(sin el) from a polynomial,
-  // no load and no special bins.
-  // warps start on multiples of 32 samples: a warp's store is then one 128-byte line per row whenever n_t % 32 == 0
-  auto phase3 = [&](auto mode_tag) {
-    constexpr int MODE = decltype(mode_tag)::value;
-    for (int64_t jb = (j0 & ~(int64_t)31) + tid; jb < j1; jb += F32_THREADS * F32_S) {
-      float a1[F32_S], a2[F32_S], a3[F32_S], se[F32_S], ce[F32_S];
-      const float4* yk[F32_S];
-      const char* oq[F32_S];  // out + j: a store is then one 64-bit add of the row's byte offset
-#pragma unroll
-      for (int q = 0; q < F32_S; q++) {
-        // a sample index outside the tile repeats the tile's first / last sample: the same value is stored to the same address
-        // by the thread that owns it, which is harmless and keeps the inner loop free of predicates
-        const int64_t j = max(min(jb + q * F32_THREADS, j1 - 1), j0);
-        const double tj = P.t_full[j];
-        int i = (int)floor((tj - t_atm0) * inv_ts);
-        i = min(max(i, k0), k1 - 1);
-        const int li = i - wa;
-        const float s = (float)(tj - P.t_atm[i]) * (splq[li].x * inv_ts_f);  // may leave [0, 1] by ~1e-6, or at the ends
-        const float hh = h26[li], c = 1.f - s;
-        a1[q] = s;
-        a2[q] = hh * (c * c * c - c);
-        a3[q] = hh * (s * s * s - s);
-        se[q] = ce[q] = 0.f;
-        if constexpr (MODE != 0) {
-          const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
-          ce[q] = (float)bf.x;
-          se[q] = (float)bf.y;
-        }
-        yk[q] = ym4 + li * F32_KS;
-        oq[q] = reinterpret_cast<const char*>(out + j);
-      }
-#pragma unroll 2
-      for (int p = 0; p < npairs; p++) {
-        const float4 uw = dc_uw[p];
-        int2 tb = make_int2(0, 0);
-        float4 cal = make_float4(0.f, 0.f, 0.f, 0.f);
-        if constexpr (MODE == 1) tb = dc_tab[p];
-        if constexpr (MODE == 2) cal = dc_cal[p];
-        const longlong2 ro = *reinterpret_cast<const longlong2*>(&dc_row[2 * p]);
-#pragma unroll
-        for (int q = 0; q < F32_S; q++) {
-          const float4 q0 = yk[q][p], q1 = yk[q][F32_KS + p];
-          const float a0 = 1.f - a1[q];
-          float2 v = __fmul2_rn(f2(a0, a0), f2(q0.x, q0.y));
-          v = __ffma2_rn(f2(a1[q], a1[q]), f2(q1.x, q1.y), v);
-          v = __ffma2_rn(f2(a2[q], a2[q]), f2(q0.z, q0.w), v);
-          v = __ffma2_rn(f2(a3[q], a3[q]), f2(q1.z, q1.w), v);
-          if constexpr (MODE == 1) {
-            const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
-            // |1 - sin el|: sin el can exceed 1 by an ulp; inputs are finite (checked by matm_set_scan / matm_set_detectors)
-            const float2 t = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));
-            const float2 x = __ffma2_rn(t, scale2, magic2);  // round(t * scale) in the low mantissa bits
-            const float2 r = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
-            const float2 dt = __ffma2_rn(t, scale2, f2(-r.x, -r.y));
-            const int i0 = __float_as_int(x.x) + tb.x, i1 = __float_as_int(x.y) + tb.y;
-            const float2 c0 = __ldg(calq + i0), c1 = __ldg(calq + i1);
-            float2 f = f2(fmaf(c0.y, dt.x, c0.x), fmaf(c1.y, dt.y, c1.x));
-            if (!(f.x * f.y == f.x * f.y)) {  // a bin with a grid point of the elevation table, or outside the table
-              if (!(f.x == f.x)) f.x = cal_factor_special(P, i0, dc_band[2 * p], sn.x, dt.x);
-              if (!(f.y == f.y)) f.y = cal_factor_special(P, i1, dc_band[2 * p + 1], sn.y, dt.y);
-            }
-            v = __fmul2_rn(v, f);
-          } else if constexpr (MODE == 2) {
-            const float2 sn = __ffma2_rn(f2(uw.x, uw.y), f2(se[q], se[q]), __fmul2_rn(f2(uw.z, uw.w), f2(ce[q], ce[q])));
-            const float2 sq = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));  // |.|: sin el may exceed 1 by an ulp
-            const float2 el = asin01_f32x2(sn, sq);
-            const float2 den = __ffma2_rn(f2(cal.z, cal.w), el, f2(cal.x, cal.y));
-            v = __fmul2_rn(v, f2(fast_rcp(den.x), fast_rcp(den.y)));
-          }
-          st_at(oq[q], ro.x, v.x);
-          st_at(oq[q], ro.y, v.y);
-        }
-      }
-      if (nd & 1) {  // odd tail detector of a partial tile; the same arithmetic as the paired path (bit-identical shards)
-        const int p = npairs;
-        const float uu = dc_uw[p].x, ww = dc_uw[p].z;
-        const int tbx = dc_tab[p].x;
-        const float hc = dc_cal[p].x, hs = dc_cal[p].z;
-        const long long r0 = dc_row[2 * p];
-#pragma unroll
-        for (int q = 0; q < F32_S; q++) {
-          const float4 q0 = yk[q][p], q1 = yk[q][F32_KS + p];
-          float v = fmaf(a3[q], q1.z, fmaf(a2[q], q0.z, fmaf(a1[q], q1.x, (1.f - a1[q]) * q0.x)));
-          if constexpr (MODE == 1) {
-            const float sn = fmaf(uu, se[q], ww * ce[q]);
-            const float t = fast_sqrt(fabsf(1.f - sn));
-            const float x = fmaf(t, MATM_CAL_SCALE, 12582912.f);
-            const float dt = fmaf(t, MATM_CAL_SCALE, -(x - 12582912.f));
-            const int i0 = __float_as_int(x) + tbx;
-            const float2 c0 = __ldg(calq + i0);
-            float f = fmaf(c0.y, dt, c0.x);
-            if (!(f == f)) f = cal_factor_special(P, i0, dc_band[2 * p], sn, dt);
-            v *= f;
-          } else if constexpr (MODE == 2) {
-            const float sn = fmaf(uu, se[q], ww * ce[q]);
-            const float sq = fast_sqrt(fabsf(1.f - sn));
-            const float2 el = asin01_f32x2(f2(sn, sn), f2(sq, sq));
-            v *= fast_rcp(fmaf(hs, el.x, hc));
-          }
-          st_at(oq[q], r0, v);
-        }
+  // the rows can go through the TMA when every row segment is 16-byte aligned in global memory (the sub-chunk grid is
+  // aligned to 128 samples, so shared and global phases agree); otherwise all threads store scalars
+  const bool bulk_ok = (P.n_t % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  uint64_t pol = 0;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  // per-pair constants, in registers for the whole tile
+  const float2 P0 = f2(dc_p0[p], dc_p0[p + 16]), P1 = f2(dc_p1[p], dc_p1[p + 16]), P2 = f2(dc_p2[p], dc_p2[p + 16]);
+  const float2 U2 = f2(dc_u[p], dc_u[p + 16]), W2 = f2(dc_w[p], dc_w[p + 16]);
+  const int tb0 = dc_tab[p], tb1 = dc_tab[p + 16], bd0 = dc_band[p], bd1 = dc_band[p + 16];
+
+  // one 16-byte record per sample of a sub-chunk: the cubic weights and x (MODE 2) or the boresight (MODE 1)
+  auto make_records = [&](int c, int buf) {
+    if (tid < F32_SUB) {
+      const int64_t j = max(min(J0 + (int64_t)c * F32_SUB + tid, j1 - 1), j0);  // outside the tile: repeat its edge sample
+      const float4 w = __ldg(P.samp_w + j);  // {a1, a2, a3, interval}
+      float x = 0.f;
+      if (mode == 2) x = (float)(P.el_full[j] - emid);
+      rec[buf * F32_SUB + tid] = make_float4(w.x, w.y, w.z, x);
+      rli[buf * F32_SUB + tid] = min(max(__float_as_int(w.w), k0), k1 - 1) - wa;
+      if (mode == 1) {
+        const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
+        rcs[buf * F32_SUB + tid] = f2((float)bf.x, (float)bf.y);
       }
     }
   };
-  if (!krj)
+  make_records(0, 0);
+  __syncthreads();
+
+  int cur = -1;
+  float2 y0 = f2(0.f, 0.f), dy = y0, m0 = y0, m1 = y0;
+  auto reload = [&](int li) {
+    const float4 q0 = ym4[li * F32_KS + p], q1 = ym4[(li + 1) * F32_KS + p];
+    y0 = f2(q0.x, q0.y);
+    dy = __fadd2_rn(f2(q1.x, q1.y), f2(-q0.x, -q0.y));
+    m0 = f2(q0.z, q0.w);
+    m1 = f2(q1.z, q1.w);
+    cur = li;
+  };
+  auto eval = [&](auto mode_tag, const float4 r, const float2 cs) -> float2 {
+    constexpr int MODE = decltype(mode_tag)::value;
+    float2 v = __ffma2_rn(f2(r.x, r.x), dy, y0);
+    v = __ffma2_rn(f2(r.y, r.y), m0, v);
+    v = __ffma2_rn(f2(r.z, r.z), m1, v);
+    if constexpr (MODE == 2) {
+      const float2 x2 = f2(r.w, r.w);
+      float2 den = __ffma2_rn(P2, x2, P1);
+      den = __ffma2_rn(den, x2, P0);
+      v = __fmul2_rn(v, f2(fast_rcp(den.x), fast_rcp(den.y)));
+    } else if constexpr (MODE == 1) {
+      const float2 sn = __ffma2_rn(U2, f2(cs.y, cs.y), __fmul2_rn(W2, f2(cs.x, cs.x)));
+      // |1 - sin el|: sin el can exceed 1 by an ulp; inputs are finite (checked by matm_set_scan / matm_set_detectors)
+      const float2 t = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));
+      const float2 x = __ffma2_rn(t, f2(MATM_CAL_SCALE, MATM_CAL_SCALE), f2(12582912.f, 12582912.f));  // round(t * scale) in the low mantissa bits
+      const float2 rr = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
+      const float2 dt = __ffma2_rn(t, f2(MATM_CAL_SCALE, MATM_CAL_SCALE), f2(-rr.x, -rr.y));
+      const int i0 = __float_as_int(x.x) + tb0, i1 = __float_as_int(x.y) + tb1;
+      const float2 c0 = __ldg(calq + i0), c1 = __ldg(calq + i1);
+      float2 f = f2(fmaf(c0.y, dt.x, c0.x), fmaf(c1.y, dt.y, c1.x));
+      if (!(f.x * f.y == f.x * f.y)) {  // a bin with a grid point of the elevation table, or outside the table
+        if (!(f.x == f.x)) f.x = cal_factor_special(P, i0, bd0, sn.x, dt.x);
+        if (!(f.y == f.y)) f.y = cal_factor_special(P, i1, bd1, sn.y, dt.y);
+      }
+      v = __fmul2_rn(v, f);
+    }
+    return v;
+  };
+
+  auto phase3 = [&](auto mode_tag) {
+    constexpr int MODE = decltype(mode_tag)::value;
+    for (int c = 0; c < n_sub; c++) {
+      const int buf = c & 1;
+      if (c + 1 < n_sub) make_records(c + 1, buf ^ 1);
+      const float4* __restrict__ rc = rec + buf * F32_SUB;
+      const int* __restrict__ rl = rli + buf * F32_SUB;
+      const float2* __restrict__ rs = rcs + buf * F32_SUB;
+      float* __restrict__ sg = stage + buf * (F32_DT * F32_RS);
+#pragma unroll
+      for (int g = 0; g < F32_SUB / 64; g++) {
+        const int col = (F32_SUB / 8) * warp + (F32_SUB / 16) * hw + 4 * g;
+        const int4 li4 = *reinterpret_cast<const int4*>(rl + col);
+        float2 v[4];
+        if (li4.x == li4.w) {  // the four samples lie in one spline interval (the usual case)
+          if (li4.x != cur) reload(li4.x);
+#pragma unroll
+          for (int q = 0; q < 4; q++) v[q] = eval(mode_tag, rc[col + q], MODE == 1 ? rs[col + q] : f2(0.f, 0.f));
+        } else {
+          const int li[4] = {li4.x, li4.y, li4.z, li4.w};
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            if (li[q] != cur) reload(li[q]);
+            v[q] = eval(mode_tag, rc[col + q], MODE == 1 ? rs[col + q] : f2(0.f, 0.f));
+          }
+        }
+        *reinterpret_cast<float4*>(sg + p * F32_RS + col) = make_float4(v[0].x, v[1].x, v[2].x, v[3].x);
+        *reinterpret_cast<float4*>(sg + (p + 16) * F32_RS + col) = make_float4(v[0].y, v[1].y, v[2].y, v[3].y);
+      }
+      // hand the sub-chunk to the TMA: writes visible to the async proxy, the other buffer's previous read finished
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      if (tid < F32_DT) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      __syncthreads();
+      const int64_t J = J0 + (int64_t)c * F32_SUB;
+      const int64_t ja = max(J, j0), jb = min(J + F32_SUB, j1);
+      if (bulk_ok) {
+        if (tid < nd) {
+          float* dst = out + dc_row[tid];
+          const float* src = sg + tid * F32_RS;
+          const int64_t ja4 = (ja + 3) & ~(int64_t)3, jb4 = jb & ~(int64_t)3;
+          if (ja4 < jb4) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst + ja4),
+                         "r"(f32_smem_u32(src + (ja4 - J))), "r"((uint32_t)(jb4 - ja4) * 4u), "l"(pol)
+                         : "memory");
+          }
+          for (int64_t j = ja; j < min(ja4, jb); j++) __stcs(dst + j, src[j - J]);
+          for (int64_t j = max(jb4, ja4); j < jb; j++) __stcs(dst + j, src[j - J]);
+        }
+        if (tid < F32_DT) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      } else {
+        const int len = (int)(jb - ja);
+        for (int e = tid; e < nd * len; e += F32_THREADS) {
+          const int r = e / len, jj = e % len;
+          __stcs(out + dc_row[r] + ja + jj, sg[r * F32_RS + (int)(ja - J) + jj]);
+        }
+      }
+    }
+    if (tid < F32_DT) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // shared memory must outlive the reads
+  };
+  if (mode == 0)
     phase3(std::integral_constant<int, 0>{});
-  else if (s_cal_ie >= 0)
+  else if (mode == 2)
     phase3(std::integral_constant<int, 2>{});
   else
     phase3(std::integral_constant<int, 1>{});
 }
 
-static size_t synth_f32_smem(int n_layers) {
-  return (size_t)F32_W * F32_KS * sizeof(float4) + F32_SPLN * sizeof(float) + F32_W * sizeof(Knot<float>) +
-         (size_t)n_layers * F32_W * sizeof(LayerKnot<float>);
+static size_t synth_f32_smem() {
+  return (size_t)F32_W * F32_KS * sizeof(float4) + (size_t)F32_W * sizeof(float4) + 2 * F32_DT * F32_RS * sizeof(float) +
+         2 * F32_SUB * (sizeof(float4) + sizeof(int) + sizeof(float2));
 }
