@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--depth", type=int, default=3, help="realisations whose AR chains are in flight underneath the synthesis")
     ap.add_argument("--chunk-mib", type=int, default=None, help="scratch per detector chunk of the two-kernel synthesis [MiB]")
     ap.add_argument("--chunk-serial", action="store_true", help="run the detector chunks of one synthesis on one stream")
+    ap.add_argument("--kernel-times", action="store_true", help="bracket every launch of the two synthesis kernels with events")
     ap.add_argument("--no-overlap", action="store_true",
                     help="generate and synthesise strictly one after the other (default: the AR chains of realisation i+1 run "
                          "underneath the synthesis kernel of realisation i)")
@@ -268,6 +269,8 @@ def run_b200(args):
     barrier()  # drains the chains of the first timed realisation too: the timed region holds exactly K of everything
     atm.check_flags()
     launches0 = ctx.launch_count
+    if args.kernel_times:
+        ctx.check(ctx.lib.matm_set_timing(ctx.h, 1))
     sampler = ClockSampler(local)
     sampler.start()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
@@ -284,6 +287,14 @@ def run_b200(args):
     total_ms = ev[0].elapsed_time(ev[1])
     synth_ms = float(np.mean([a.elapsed_time(b) for a, b in syn]))
     status = atm.check_flags()
+    per_kernel = None
+    if args.kernel_times:
+        import ctypes as C
+        a, b, nch = C.c_double(), C.c_double(), C.c_int64()
+        ctx.check(ctx.lib.matm_get_timing(ctx.h, C.byref(a), C.byref(b), C.byref(nch)))
+        ctx.check(ctx.lib.matm_set_timing(ctx.h, 0))
+        per_kernel = {"loading_f32_kernel_ms": a.value / args.steps, "synth_eval_f32_kernel_ms": b.value / args.steps,
+                      "chunks_per_step": nch.value // args.steps}
     if world > 1:
         t = torch.tensor([total_ms, synth_ms], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -307,7 +318,7 @@ def run_b200(args):
         pass
     roofline = {"bound": "hbm", "kernel": "synth_f32_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                "kernel_ms": synth_ms, "step_ms_outside_kernel": ms_per_step - synth_ms}
+                "kernel_ms": synth_ms, "step_ms_outside_kernel": ms_per_step - synth_ms, "per_kernel": per_kernel}
 
     # ---- end to end through the public API with HOST buffers ----
     e2e = None

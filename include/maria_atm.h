@@ -133,6 +133,13 @@ int matm_synthesize(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, 
  * overlap != 0 alternates consecutive chunks between two scratch buffers and two internal streams.  Defaults: 32, 1. */
 int matm_set_tuning(matm_handle* h, int chunk_mib, int overlap);
 
+/* Per-kernel timing of the float path (measurement only): with enable != 0 every chunk's two launches are bracketed by
+ * CUDA events on the stream they run on; matm_get_timing synchronises the device, returns the summed durations [ms] of the
+ * loading and the evaluation kernels since the last call (they overlap in wall time when chunks alternate between the two
+ * internal streams) and resets the counters. */
+int matm_set_timing(matm_handle* h, int enable);
+int matm_get_timing(matm_handle* h, double* loading_ms, double* eval_ms, int64_t* n_chunks);
+
 /* Same, delivering into HOST memory (pinned or pageable): detector-chunked, device->host copies overlapped with
  * the kernels of the next chunk.  Synchronises before returning. */
 int matm_synthesize_host(matm_handle* h, int64_t det0, int64_t n_det, void* out_host, int units, int apply_gain);

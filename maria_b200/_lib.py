@@ -46,6 +46,8 @@ SIGNATURES = {
     "matm_upsample_linear": (C.c_int, [vp, vp, C.c_int64, vp, vp]),
     "matm_synthesize": (C.c_int, [vp, C.c_int64, C.c_int64, vp, C.c_int, C.c_int, vp]),
     "matm_set_tuning": (C.c_int, [vp, C.c_int, C.c_int]),
+    "matm_set_timing": (C.c_int, [vp, C.c_int]),
+    "matm_get_timing": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "matm_synthesize_host": (C.c_int, [vp, C.c_int64, C.c_int64, vp, C.c_int, C.c_int]),
     "matm_calibrate": (C.c_int, [vp, C.c_int64, C.c_int64, vp, vp, C.c_int, vp]),
     "matm_check_flags": (C.c_int, [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64),

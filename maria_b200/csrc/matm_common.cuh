@@ -13,11 +13,11 @@
 #include "../../include/maria_atm.h"
 
 #define MATM_ABI_VERSION 1
-#define MATM_CAL_SCALE 4096.0f  // bins per unit of t = sqrt(1 - sin el) in the fp32 calibration table
 
 // Device-side layer descriptor: everything the sampler needs per layer, in cell units.
 struct LayerDev {
   const void* data;   // (n_ext, n_cs) row-major, float or double
+  void* data2;        // fp32 handles: (n_ext, n_cs) float2 = {v[i][j], v[i][j+1]}, refreshed from `data` by every synthesis
   const double* base; // (n_t_atm, 2): boresight position in the layer grid, in cells (f64)
   int n_ext, n_cs;
   double D[4];        // 2x2: cells per unit of (pp_d - pp_b): [x<-x, x<-y, y<-x, y<-y]
@@ -67,12 +67,6 @@ struct SynthParams {
   const void* G2_R;        // (n_bands, npwv, nel)
   const void* Hc_R;        // (n_bands, nel-1): H(el) = Hc + Hs * el on el-interval i  (same line as the lerp of H1)
   const void* Hs_R;        // (n_bands, nel-1)
-  // fp32 fast path of a14: 1 / (factor k_B 1e12 H(el)) as one straight line per bin of t = sqrt(1 - sin el), bins of
-  // width 1 / MATM_CAL_SCALE (see build_cal_table in matm_setup.cu)
-  const float2* calq;      // (n_bands, calq_n): {c0, c1}, value = c0 + c1 dt, dt in [-1/2, 1/2]; c1 = NaN marks a special bin
-  const int* calq_kind;    // (n_bands, calq_n): 0 plain bin, k > 0 record k of calq_aux, < 0 generic slow path
-  const float4* calq_aux;  // 2 float4 per record: {c0, c1 for dt <= dt_k, c0, c1 for dt > dt_k}, {dt_k, 0, 0, 0}
-  int calq_n;
   float pwv_lo_f, pwv_hi_f, el_lo_f, el_hi_f;  // ends of the fp32 (pwv, el) grids
   float det_rmax_f;        // largest angular distance of a detector (rolled offsets) from the boresight [rad]
   double det_rmax;
@@ -99,18 +93,20 @@ struct matm_handle {
   float* yk_buf[2] = {nullptr, nullptr};
   size_t yk_bytes = 0;
   bool yk_used = false;
+  // optional per-kernel timing of the float synthesis (matm_set_timing / matm_get_timing): events around every launch
+  bool timing = false;
+  std::vector<cudaEvent_t> tev;  // triples (before loading, between, after evaluation) per chunk
+  size_t tev_used = 0;
   int chunk_mib = 32;   // scratch per chunk; two chunks in flight must fit the 126 MB L2 next to the layers
   bool overlap = true;  // alternate chunks between two side streams
   cudaStream_t yk_stream[2] = {nullptr, nullptr};
   cudaEvent_t yk_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   double* layer_base[MATM_MAX_LAYERS] = {};
+  float2* layer_pairs[MATM_MAX_LAYERS] = {};  // pair-expanded copies of the smoothed layers (fp32 handles)
   double *det_atm = nullptr, *det_full = nullptr, *mueller00 = nullptr, *gain = nullptr;
   int32_t* band_index = nullptr;
   double *side_pwv = nullptr, *side_el = nullptr, *G2 = nullptr, *H1 = nullptr;
   void* tabR = nullptr;  // one allocation holding the R-typed tables
-  float2* calq = nullptr;
-  int* calq_kind = nullptr;
-  float4* calq_aux = nullptr;
   // processing order of the detectors of a requested range (spatially coherent tiles; matm_detector_order)
   std::vector<double> det_xy_host;  // (n_det, 2) the atmosphere's offsets, kept for the ordering
   struct DetOrder {

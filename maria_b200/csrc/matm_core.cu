@@ -49,7 +49,11 @@ extern "C" int matm_destroy(matm_handle* h) {
   }
   for (int i = 0; i < 4; i++)
     if (h->yk_ev[i]) cudaEventDestroy(h->yk_ev[i]);
-  for (int l = 0; l < MATM_MAX_LAYERS; l++) cudaFree(h->layer_base[l]);
+  for (cudaEvent_t e : h->tev) cudaEventDestroy(e);
+  for (int l = 0; l < MATM_MAX_LAYERS; l++) {
+    cudaFree(h->layer_base[l]);
+    cudaFree(h->layer_pairs[l]);
+  }
   cudaFree(h->det_atm);
   cudaFree(h->det_full);
   cudaFree(h->mueller00);
@@ -60,13 +64,10 @@ extern "C" int matm_destroy(matm_handle* h) {
   cudaFree(h->G2);
   cudaFree(h->H1);
   cudaFree(h->tabR);
-  cudaFree(h->calq);
-  cudaFree(h->calq_kind);
   for (auto& kv : h->det_order) {
     cudaFree(kv.second.order);
     cudaFree(kv.second.tile_m);
   }
-  cudaFree(h->calq_aux);
   cudaFree(h->flags);
   for (int i = 0; i < 2; i++) {
     cudaFree(h->stage_dev[i]);

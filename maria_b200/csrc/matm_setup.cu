@@ -281,6 +281,9 @@ extern "C" int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_de
     MATM_LAUNCHED(h);
     MATM_CUDA(h, cudaDeviceSynchronize());
     LayerDev& o = P.layers[l];
+    if (h->dtype == MATM_F32)
+      if ((rc = matm_upload(h, &h->layer_pairs[l], (const float2*)nullptr, (size_t)d.n_ext * d.n_cs))) return rc;
+    o.data2 = h->layer_pairs[l];
     o.data = d.data_dev;
     o.base = h->layer_base[l];
     o.n_ext = d.n_ext;
@@ -557,78 +560,6 @@ __global__ void typed_tables_kernel(const double* __restrict__ pwv, const double
 }
 
 
-// ---------------------------------------------------------------------------------------------------------
-// fp32 fast path of a14 (tod.py:106-142 -> band.py:235-255): the factor 1 / (factor k_B 1e12 H(el)) as a function of
-// t = sqrt(1 - sin el), tabulated as one straight line per bin of width 1 / MATM_CAL_SCALE.  el(t) = pi/2 - 2 asin(t / sqrt 2)
-// is analytic on the whole range (no singularity at the zenith), H is the reference's piecewise-linear interpolant of
-// the folded transmission integral on the elevation grid, so inside a bin that holds no grid point the function is
-// smooth and the line through the two Chebyshev nodes is off by f'' / (16 SCALE^2) ~ 4e-9 f''.  A bin that holds exactly
-// one interior grid point gets two lines (aux record, selected by comparing dt with the kink position); every other
-// case (outside the table, several grid points in one bin, table not covering T0 / pwv) is kind < 0 and is evaluated by
-// the generic code, which also raises the flags.  Special bins carry c1 = NaN so that the fast path notices them.
-// ---------------------------------------------------------------------------------------------------------
-static double cal_el_of_t(double t) { return M_PI / 2 - 2 * asin(fmin(fabs(t) / M_SQRT2, 1.0)); }
-
-static void cal_fit(const double* el, const double* H, int iv, double tc, double width, float* c) {
-  // line in dt (bin units, centre tc, dt in [-1/2, 1/2]) through the Chebyshev nodes, on the linear piece `iv` of H
-  const double a = 0.35355339059327373;  // cos(pi / 4) / 2
-  double f[2];
-  for (int q = 0; q < 2; q++) {
-    const double e = cal_el_of_t(tc + (q ? a : -a) * width);
-    f[q] = 1.0 / (H[iv] + (H[iv + 1] - H[iv]) * (e - el[iv]) / (el[iv + 1] - el[iv]));
-  }
-  c[0] = (float)(0.5 * (f[0] + f[1]));
-  c[1] = (float)((f[1] - f[0]) / (2 * a));
-}
-
-static void build_cal_table(const double* el, int nel, const double* H1, int n_bands, bool table_ok, int* n_per_band,
-                            std::vector<float>& tab, std::vector<int>& kind, std::vector<float>& aux) {
-  const double scale = MATM_CAL_SCALE;
-  const int n = (int)ceil(M_SQRT2 * scale) + 3;  // t <= sqrt 2
-  *n_per_band = n;
-  tab.assign((size_t)n_bands * n * 2, 0.f);
-  kind.assign((size_t)n_bands * n, 0);
-  aux.assign(8, 0.f);  // record 0 is unused (kind 0 means "plain bin")
-  const float qnan = nanf("");
-  for (int b = 0; b < n_bands; b++) {
-    const double* H = H1 + (size_t)b * nel;
-    for (int r = 0; r < n; r++) {
-      float* c = &tab[((size_t)b * n + r) * 2];
-      int& kd = kind[(size_t)b * n + r];
-      const double tc = r / scale, half = 0.5 / scale;
-      const double t_lo = fmax(tc - half, 0.0), t_hi = tc + half;
-      const double e_hi = cal_el_of_t(t_lo), e_lo = t_hi >= M_SQRT2 ? -M_PI / 2 : cal_el_of_t(t_hi);  // el falls as t grows
-      const bool slow = !table_ok || e_lo < el[0] || e_hi > el[nel - 1];
-      int first = -1, count = 0;  // interior grid points inside the bin (closed, with a margin for the fp32 rounding of t)
-      const double margin = 1e-6;
-      for (int i = 1; i <= nel - 2; i++)
-        if (el[i] >= e_lo - margin && el[i] <= e_hi + margin) {
-          if (count == 0) first = i;
-          count++;
-        }
-      if (slow || count > 1) {
-        c[0] = c[1] = qnan;
-        kd = -1;
-      } else if (count == 0) {
-        int iv = 0;
-        const double ec = cal_el_of_t(tc);
-        while (iv < nel - 2 && el[iv + 1] < ec) iv++;
-        cal_fit(el, H, iv, tc, 2 * half, c);
-      } else {
-        // the kink el[first] sits at t_k; for t <= t_k (higher elevation) the piece is `first`, beyond it `first - 1`
-        const double t_k = sqrt(fmax(1.0 - sin(el[first]), 0.0));
-        float rec[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        cal_fit(el, H, first, tc, 2 * half, rec);
-        cal_fit(el, H, first - 1, tc, 2 * half, rec + 2);
-        rec[4] = (float)((t_k - tc) * scale);
-        kd = (int)(aux.size() / 8);
-        aux.insert(aux.end(), rec, rec + 8);
-        c[0] = c[1] = qnan;
-      }
-    }
-  }
-}
-
 extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int nel, int nnu, const double* side_T_host,
                               const double* side_pwv_host, const double* side_el_host, const double* side_nu_host,
                               const double* emission_host, const double* opacity_host, const double* passband_host,
@@ -701,21 +632,6 @@ extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int
   P.pwv_hi_f = (float)side_pwv_host[npwv - 1];
   P.el_lo_f = (float)side_el_host[0];
   P.el_hi_f = (float)side_el_host[nel - 1];
-  if (h->dtype == MATM_F32) {
-    std::vector<double> H1h((size_t)n_bands * nel);
-    MATM_CUDA(h, cudaMemcpy(H1h.data(), h->H1, H1h.size() * sizeof(double), cudaMemcpyDeviceToHost));
-    std::vector<float> tab, aux;
-    std::vector<int> kind;
-    int n_per_band = 0;
-    build_cal_table(side_el_host, nel, H1h.data(), n_bands, okc, &n_per_band, tab, kind, aux);
-    if ((rc = matm_upload(h, (float**)&h->calq, tab.data(), tab.size()))) return rc;
-    if ((rc = matm_upload(h, &h->calq_kind, kind.data(), kind.size()))) return rc;
-    if ((rc = matm_upload(h, (float**)&h->calq_aux, aux.data(), aux.size()))) return rc;
-    P.calq = h->calq;
-    P.calq_kind = h->calq_kind;
-    P.calq_aux = h->calq_aux;
-    P.calq_n = n_per_band;
-  }
   h->have_bands = true;
   return MATM_OK;
 }

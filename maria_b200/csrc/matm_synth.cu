@@ -315,11 +315,23 @@ static int launch_synth_f32(matm_handle* h, int64_t det0, int64_t n_det, float* 
   for (int i = 0; i < 4; i++)
     if (!h->yk_ev[i]) MATM_CUDA(h, cudaEventCreateWithFlags(&h->yk_ev[i], cudaEventDisableTiming));
   const size_t smem = synth_f32_smem();
-  MATM_CUDA(h, cudaFuncSetAttribute(synth_eval_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // the 4-samples-per-thread kernel needs at most one knot inside any 4 consecutive samples
+  const bool fast = h->min_samples_per_interval >= 4 && P.n_t < ((int64_t)1 << 30) && n_det < ((int64_t)1 << 31);
+  auto eval_kernel = fast ? synth_eval_f32_kernel : synth_eval_general_f32_kernel;
+  MATM_CUDA(h, cudaFuncSetAttribute(eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // the scratch buffers are shared by every call on this handle: order this call after the previous one
   if (h->yk_used) {
     MATM_CUDA(h, cudaStreamWaitEvent(st, h->yk_ev[3], 0));
   }
+  {  // the sampler reads the smoothed layers through their pair-expanded copy
+    int max_cells = 1;
+    for (int l = 0; l < P.n_layers; l++) max_cells = max(max_cells, P.layers[l].n_ext * P.layers[l].n_cs);
+    dim3 grid((unsigned)min(4 * h->sm_count, (max_cells + 255) / 256), (unsigned)P.n_layers);
+    expand_layers_kernel<<<grid, 256, 0, st>>>(P);
+    MATM_LAUNCHED(h);
+  }
+  const size_t smem_a = (size_t)P.n_layers * LD_KA * sizeof(int4);
+  MATM_CUDA(h, cudaFuncSetAttribute(loading_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a));
   if (two) {
     MATM_CUDA(h, cudaEventRecord(h->yk_ev[0], st));
     MATM_CUDA(h, cudaStreamWaitEvent(h->yk_stream[0], h->yk_ev[0], 0));
@@ -329,10 +341,23 @@ static int launch_synth_f32(matm_handle* h, int64_t det0, int64_t n_det, float* 
     const int64_t t0 = c * chunk, nt = min(chunk, n_tiles - t0);
     cudaStream_t s = two ? h->yk_stream[c & 1] : st;
     float* yk = h->yk_buf[two ? (c & 1) : 0];
-    loading_f32_kernel<<<(unsigned)(nt * n_kb), LD_THREADS, 0, s>>>(P, order, tile_m, t0, n_det, yk, apply_gain);
+    cudaEvent_t* te = nullptr;
+    if (h->timing) {
+      while (h->tev.size() < h->tev_used + 3) {
+        cudaEvent_t e;
+        MATM_CUDA(h, cudaEventCreate(&e));
+        h->tev.push_back(e);
+      }
+      te = &h->tev[h->tev_used];
+      h->tev_used += 3;
+      MATM_CUDA(h, cudaEventRecord(te[0], s));
+    }
+    loading_f32_kernel<<<(unsigned)(nt * n_kb), LD_THREADS, smem_a, s>>>(P, order, tile_m, t0, n_det, yk, apply_gain);
     MATM_LAUNCHED(h);
-    synth_eval_f32_kernel<<<(unsigned)(nt * n_tt), F32_THREADS, smem, s>>>(P, order, t0, det0, n_det, yk, out, units);
+    if (te) MATM_CUDA(h, cudaEventRecord(te[1], s));
+    eval_kernel<<<(unsigned)(nt * n_tt), F32_THREADS, smem, s>>>(P, order, t0, det0, n_det, yk, out, units);
     MATM_LAUNCHED(h);
+    if (te) MATM_CUDA(h, cudaEventRecord(te[2], s));
   }
   if (two) {
     for (int i = 0; i < 2; i++) {
@@ -395,6 +420,32 @@ extern "C" int matm_set_tuning(matm_handle* h, int chunk_mib, int overlap) {
   if (chunk_mib < 1 || chunk_mib > 65536) MATM_FAIL_ARG(h, "matm_set_tuning: chunk_mib must be in [1, 65536]");
   h->chunk_mib = chunk_mib;
   h->overlap = overlap != 0;
+  return MATM_OK;
+}
+
+extern "C" int matm_set_timing(matm_handle* h, int enable) {
+  MATM_CHECK_HANDLE(h);
+  h->timing = enable != 0;
+  h->tev_used = 0;
+  return MATM_OK;
+}
+
+extern "C" int matm_get_timing(matm_handle* h, double* loading_ms, double* eval_ms, int64_t* n_chunks) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  MATM_CUDA(h, cudaDeviceSynchronize());
+  double a = 0.0, b = 0.0;
+  for (size_t i = 0; i + 2 < h->tev_used + 0 && i + 2 < h->tev.size() + 0; i += 3) {
+    float ms = 0.f;
+    MATM_CUDA(h, cudaEventElapsedTime(&ms, h->tev[i], h->tev[i + 1]));
+    a += ms;
+    MATM_CUDA(h, cudaEventElapsedTime(&ms, h->tev[i + 1], h->tev[i + 2]));
+    b += ms;
+  }
+  if (loading_ms) *loading_ms = a;
+  if (eval_ms) *eval_ms = b;
+  if (n_chunks) *n_chunks = (int64_t)(h->tev_used / 3);
+  h->tev_used = 0;
   return MATM_OK;
 }
 

@@ -8,10 +8,10 @@
 //                                      -> yk[tile][knot][32 slots] (an L2-sized scratch of the chunk, no halo, own occupancy)
 //   synth_eval_f32_kernel (per sample) window of yk -> shared memory; not-a-knot cubic spline second derivatives by the
 //                                      windowed Thomas sweep; evaluation + pW -> K_RJ at the full-rate samples: thread =
-//                                      F32_S samples, loop over detector PAIRS in packed f32x2 arithmetic.  The calibration
-//                                      factor is rcp of a QUADRATIC in the boresight elevation with per-(detector, tile)
-//                                      coefficients (every transcendental depends on time only through el_b), else the
-//                                      t = sqrt(1 - sin el) table of matm_setup.cu.
+//                                      4 consecutive samples, loop over the detectors, packed f32x2 arithmetic over sample
+//                                      pairs, one 16-byte store per detector.  The calibration factor is rcp of a QUADRATIC
+//                                      in the boresight elevation with per-(detector, tile) coefficients (every
+//                                      transcendental depends on time only through el_b), else the exact search + asin.
 #pragma once
 #include <type_traits>
 #include "matm_synth.cuh"
@@ -19,9 +19,10 @@
 #define F32_DT 32
 #define F32_THREADS 256
 #ifndef F32_KT
-// spline intervals per tile of the evaluation kernel: its window of F32_KT + 1 + 2 F32_HALO knots x 16 pairs x 16 bytes
-// plus the 38 KB of staging / records decide how many CTAs fit an SM (96: 70 KB, three CTAs); any value is correct.
-#define F32_KT 96
+// spline intervals per tile of the evaluation kernel.  Its loop over aligned groups of 4 samples is quantised in passes of
+// 256 groups: 135 intervals are 3051 samples = 2.98 passes at the C4 cadence (22.6 samples per interval); the window of
+// F32_KT + 1 + 2 F32_HALO knots x 32 detectors x 8 bytes is 42 KB.  Any value is correct (-DF32_KT=... retunes).
+#define F32_KT 135
 #endif
 #ifndef F32_HALO
 #define F32_HALO 10  // extra knots each side; the error of the artificial boundary decays as (2 - sqrt 3)^HALO
@@ -30,19 +31,25 @@
 #define F32_MINB 3   // CTAs per SM the register allocation is held to
 #endif
 #define F32_W (F32_KT + 1 + 2 * F32_HALO)
-#define F32_NP (F32_DT / 2)  // detector pairs per tile
-#ifndef F32_KS
-#define F32_KS F32_NP  // float4 entries per knot row of ym4 (padding the rows by one entry was measured: no gain, 5.21 vs 5.09 ms)
+// row stride of the {y, M} window in shared memory, in float2: the 32 lanes of a warp read 5-6 different knot rows at
+// once (128 consecutive samples), and rows 256 bytes apart would all fall on the same banks (ncu: 93 % of the L1 data
+// pipe, 1.2e9 bank conflicts); 34 shifts consecutive rows by 4 banks and keeps 16-byte alignment
+#define F32_YS (F32_DT + 2)
+#ifndef F32_UNROLL
+#define F32_UNROLL 4  // detectors per unrolled body of the evaluation loop
 #endif
 #ifndef F32_G
-#define F32_G 4  // knots per thread and iteration in phase 1
+#define F32_G 2  // knots per thread and pass of the loading kernel
+#endif
+#ifndef F32_LB
+#define F32_LB 2  // layers whose gathers are in flight together (2 F32_G F32_LB loads per thread)
 #endif
 
 struct LayerF {  // per-layer constants, two 16-byte shared-memory loads + the pointer
-  float D0, D1, D2, D3;
+  float D0, D2, D1, D3;  // (cell x, cell y) = D0, D2 per unit of pp_x and D1, D3 per unit of pp_y: packed pairs
   float rms;
   int ne1, nc1, n_cs;  // n_ext - 1, n_cs - 1, n_cs
-  const float* data;
+  const float2* data2;  // pair-expanded layer: data2[i n_cs + j] = {v[i][j], v[i][j + 1]}
   int pad[2];
 };
 
@@ -57,12 +64,6 @@ __device__ __forceinline__ float fast_rcp(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
-// *(sample_ptr + row_bytes) = v: the per-thread pointer already holds out + j, the row offset is the tile's constant
-__device__ __forceinline__ void st_at(const char* sample_ptr, long long row_bytes, float v) {
-  const char* a;
-  asm("add.s64 %0, %1, %2;" : "=l"(a) : "l"(sample_ptr), "l"(row_bytes));
-  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(a), "f"(v) : "memory");
-}
 // asin on [-1, 1]: pi/2 - sqrt(1 - |x|) P7(|x|)  (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 rad)
 __device__ __forceinline__ float fast_asin(float x) {
   const float a = fabsf(x);
@@ -76,23 +77,6 @@ __device__ __forceinline__ float fast_asin(float x) {
   p = fmaf(p, a, 1.5707963050f);
   const float r = fmaf(-fast_sqrt(fmaxf(1.0f - a, 0.0f)), p, 1.5707963268f);
   return copysignf(r, x);
-}
-
-// The calibration factor in a special bin of the table (calq_kind != 0): a bin holding one grid point of the elevation
-// table has two lines, selected by the kink position; anything else goes through the exact searching code, which also
-// raises the flag when the elevation leaves the table.
-__device__ __noinline__ float cal_factor_special(const SynthParams& P, int idx, int band, float sin_el, float dt) {
-  const int kind = P.calq_kind[idx];
-  if (kind > 0) {
-    const float4 a = __ldg(P.calq_aux + 2 * kind), k = __ldg(P.calq_aux + 2 * kind + 1);
-    return dt > k.x ? fmaf(a.w, dt, a.z) : fmaf(a.y, dt, a.x);
-  }
-  int ie = 0;
-  const int ho = band * (P.nel - 1);
-  const float den = cal_denominator<float>(P, reinterpret_cast<const float*>(P.sinel_R),
-                                           reinterpret_cast<const float*>(P.Hc_R) + ho,
-                                           reinterpret_cast<const float*>(P.Hs_R) + ho, sin_el, ie);
-  return 1.0f / den;
 }
 
 // a11 + a12 for this kernel, in two parts.  The cell of the folded (pwv, el) grid and the two weights depend on the line of
@@ -158,22 +142,37 @@ __device__ __forceinline__ float emission_blend_f32(const SynthParams& P, int ba
 #define LD_KA 128  // knots per CTA: 1 (M = 4), 2 (M = 2) or 4 (M = 1) passes of F32_G knots per thread
 #endif
 #ifndef LD_MINB
-#define LD_MINB 3
+// CTAs per SM the register allocation is held to.  Measured at C4 (ms per launch): G x LB x MINB = 2x2x4 8.1, 4x1x3 8.6,
+// 4x2x3 9.4, 2x4x3 9.7, 1x8x3 9.9, 2x4x4 10.4, 4x4x2 12.0: more warps beat more loads in flight per warp.
+#define LD_MINB 4
 #endif
+
+// One 8-byte load per grid row instead of two 4-byte loads: the sampler reads the layers through their pair-expanded copy
+// (written from the smoothed layers at the start of every synthesis; 2 x 26 MB at C4, L2-resident).
+__global__ void __launch_bounds__(256) expand_layers_kernel(const __grid_constant__ SynthParams P) {
+  const LayerDev& L = P.layers[blockIdx.y];
+  const float* __restrict__ v = reinterpret_cast<const float*>(L.data);
+  float2* __restrict__ o = reinterpret_cast<float2*>(L.data2);
+  const int n_cs = L.n_cs;
+  const int64_t total = (int64_t)L.n_ext * n_cs;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(e % n_cs);
+    const float a = v[e];
+    o[e] = make_float2(a, j + 1 < n_cs ? v[e + 1] : a);
+  }
+}
 
 template <int M>
 __device__ __forceinline__ void loading_tile_f32(const SynthParams& P, const int32_t* __restrict__ order, int64_t dbase, int nd,
-                                                 int ka, int Wn, int n_layers, const LayerF* ls, const float* dc_gain,
-                                                 const int* dc_band, const float* dc_mu, float* __restrict__ yrow, int lane,
-                                                 int warp) {
+                                                 int ka, int Wn, int n_layers, const LayerF* ls, const int4* lks,
+                                                 const float* dc_gain, const int* dc_band, const float* dc_mu,
+                                                 float* __restrict__ yrow, int lane, int warp) {
   constexpr int PL = 32 / M;
   const int slot0 = (lane % PL) * M, sub = lane / PL;
   const int64_t d = order[dbase + min(slot0, nd - 1)];  // idle lanes of a partial tile shadow the last detector
   const double* da = P.det_atm + 4 * d;
   const float u = (float)da[0], Y = (float)da[1], wm1 = (float)da[2];
   const float pwv0 = (float)P.pwv0;
-  const LayerKnot<float>* __restrict__ lk = reinterpret_cast<const LayerKnot<float>*>(P.lk_tab);
-  const int n = P.n_t_atm;
   int ip = 0, ie = 0;
   constexpr int NW = (LD_THREADS / 32) * M;
   // one pass = G knots per thread, NW * G knots per CTA.  Full passes use F32_G; what is left at the end of the block
@@ -181,12 +180,12 @@ __device__ __forceinline__ void loading_tile_f32(const SynthParams& P, const int
   auto pass = [&](auto gtag, const int kb) {
     constexpr int G = decltype(gtag)::value;
     float dppx[G], dppy[G], sinel[G], acc[G];
-    int kk[G];
+    int kk[G];  // knot within the block
     bool bad = false;
 #pragma unroll
     for (int q = 0; q < G; q++) {
-      kk[q] = ka + min(kb + q * NW, Wn - 1);  // a short last group repeats the last knot (same value, same slot)
-      const float4 kc = __ldg(P.knot_f + kk[q]);  // ce, se, ca, sa
+      kk[q] = min(kb + q * NW, Wn - 1);  // a short last group repeats the last knot (same value, same slot)
+      const float4 kc = __ldg(P.knot_f + ka + kk[q]);  // ce, se, ca, sa
       // direction of the detector minus direction of the boresight, horizon frame (coords/transforms.py:10-29)
       const float dX = u * kc.x - wm1 * kc.y;
       const float dZ = u * kc.y + wm1 * kc.x;
@@ -202,58 +201,64 @@ __device__ __forceinline__ void loading_tile_f32(const SynthParams& P, const int
       bad = bad || !(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]);
     }
     unsigned badmask = 0;
-    for (int l = 0; l < n_layers; l++) {
-      const float4 Dm = *reinterpret_cast<const float4*>(&ls[l].D0);
-      const int4 Ln = *reinterpret_cast<const int4*>(&ls[l].rms);
-      const float* data = ls[l].data;
-      float wx[G], wy[G];
-      const float* v[G];
+    // The kernel is bound by the latency of the gathers (the layers live in L2): F32_LB layers are taken at a time, all
+    // their 2 G F32_LB loads are issued before the first is used.
+    for (int l0 = 0; l0 < n_layers; l0 += F32_LB) {
+      float2 w[F32_LB][G], r0[F32_LB][G], r1[F32_LB][G];
+      float rms[F32_LB];
 #pragma unroll
-      for (int q = 0; q < G; q++) {
-        const int4 braw = __ldg(reinterpret_cast<const int4*>(lk + (size_t)l * n + kk[q]));
-        const float bfx = __int_as_float(braw.z), bfy = __int_as_float(braw.w);
-        const float fx = fmaf(Dm.x, dppx[q], fmaf(Dm.y, dppy[q], bfx));
-        const float fy = fmaf(Dm.z, dppx[q], fmaf(Dm.w, dppy[q], bfy));
-        const float flx = floorf(fx), fly = floorf(fy);
-        int ix = braw.x + (int)flx, iy = braw.y + (int)fly;
-        wx[q] = fx - flx;
-        wy[q] = fy - fly;
-        if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
-          // rare: exactly on the last grid line is inside (RGI clips the index to n - 2); anything else is outside
-          if (ix == Ln.y && wx[q] == 0.f) {
-            ix--;
-            wx[q] = 1.f;
-          }
-          if (iy == Ln.z && wy[q] == 0.f) {
-            iy--;
-            wy[q] = 1.f;
-          }
+      for (int i = 0; i < F32_LB; i++) {
+        const int l = min(l0 + i, n_layers - 1);  // a short last block repeats the last layer with weight zero
+        const float4 Dm = *reinterpret_cast<const float4*>(&ls[l].D0);  // D0, D2, D1, D3
+        const int4 Ln = *reinterpret_cast<const int4*>(&ls[l].rms);
+        const float2* __restrict__ data2 = ls[l].data2;
+        const int4* __restrict__ lkl = lks + l * LD_KA;
+        rms[i] = l0 + i < n_layers ? __int_as_float(Ln.x) : 0.f;
+#pragma unroll
+        for (int q = 0; q < G; q++) {
+          const int4 b = lkl[kk[q]];  // {ix, iy, fx, fy} of the boresight in this layer's grid
+          // (cell x, cell y) of the line of sight relative to the boresight's cell, both components at once
+          const float2 f = __ffma2_rn(f2(dppx[q], dppx[q]), f2(Dm.x, Dm.y),
+                                      __ffma2_rn(f2(dppy[q], dppy[q]), f2(Dm.z, Dm.w), f2(__int_as_float(b.z), __int_as_float(b.w))));
+          const float2 fl = f2(floorf(f.x), floorf(f.y));
+          int ix = b.x + (int)fl.x, iy = b.y + (int)fl.y;
+          w[i][q] = __fadd2_rn(f, f2(-fl.x, -fl.y));
           if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
-            record_out_of_grid(P.flags, l, d, kk[q]);  // atmosphere.py:368-369
-            badmask |= 1u << q;
-            ix = iy = 0;
+            // rare: exactly on the last grid line is inside (RGI clips the index to n - 2); anything else is outside
+            if (ix == Ln.y && w[i][q].x == 0.f) {
+              ix--;
+              w[i][q].x = 1.f;
+            }
+            if (iy == Ln.z && w[i][q].y == 0.f) {
+              iy--;
+              w[i][q].y = 1.f;
+            }
+            if ((unsigned)ix >= (unsigned)Ln.y || (unsigned)iy >= (unsigned)Ln.z) {
+              if (l0 + i < n_layers) {
+                record_out_of_grid(P.flags, l, d, ka + kk[q]);  // atmosphere.py:368-369
+                badmask |= 1u << q;
+              }
+              ix = iy = 0;
+            }
           }
+          const unsigned idx = (unsigned)(ix * Ln.w + iy);
+          r0[i][q] = __ldg(data2 + idx);                  // {v00, v01}
+          r1[i][q] = __ldg(data2 + idx + (unsigned)Ln.w);  // {v10, v11}
         }
-        v[q] = data + (ix * Ln.w + iy);
-      }
-      float v00[G], v01[G], v10[G], v11[G];
-#pragma unroll
-      for (int q = 0; q < G; q++) {
-        v00[q] = __ldg(v[q]);
-        v01[q] = __ldg(v[q] + 1);
-        v10[q] = __ldg(v[q] + Ln.w);
-        v11[q] = __ldg(v[q] + Ln.w + 1);
       }
 #pragma unroll
-      for (int q = 0; q < G; q++) {
-        const float a = fmaf(wy[q], v01[q] - v00[q], v00[q]), bb = fmaf(wy[q], v11[q] - v10[q], v10[q]);
-        acc[q] = fmaf(__int_as_float(Ln.x), fmaf(wx[q], bb - a, a), acc[q]);
-      }
+      for (int i = 0; i < F32_LB; i++)
+#pragma unroll
+        for (int q = 0; q < G; q++) {
+          // along the extrusion axis first, on both columns at once; then across
+          const float2 c = __ffma2_rn(f2(w[i][q].x, w[i][q].x), __fadd2_rn(r1[i][q], f2(-r0[i][q].x, -r0[i][q].y)), r0[i][q]);
+          acc[q] = fmaf(rms[i], fmaf(w[i][q].y, c.y - c.x, c.x), acc[q]);
+        }
     }
 #pragma unroll
     for (int q = 0; q < G; q++) {
       if (bad || ((badmask >> q) & 1)) {
-        if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, kk[q]);
+        if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q])) record_out_of_grid(P.flags, 0, d, ka + kk[q]);
         if (!(dppx[q] == dppx[q]) || !(dppy[q] == dppy[q]) || ((badmask >> q) & 1)) acc[q] = r_nan<float>();
       }
       float wp, we;
@@ -267,7 +272,7 @@ __device__ __forceinline__ void loading_tile_f32(const SynthParams& P, const int
         if (sl >= nd) y[j] = 0.f;  // unused slots of a partial tile
       }
       if (kb + q * NW < Wn) {
-        float* o = yrow + (size_t)kk[q] * F32_DT + slot0;
+        float* o = yrow + (size_t)(ka + kk[q]) * F32_DT + slot0;
         if constexpr (M == 1) *o = y[0];
         if constexpr (M == 2) *reinterpret_cast<float2*>(o) = make_float2(y[0], y[1]);
         if constexpr (M == 4) *reinterpret_cast<float4*>(o) = make_float4(y[0], y[1], y[2], y[3]);
@@ -277,12 +282,13 @@ __device__ __forceinline__ void loading_tile_f32(const SynthParams& P, const int
   const int vw = warp * M + sub;
   for (int base = 0; base < Wn;) {
     const int rem = Wn - base;
-    if (rem > (F32_G / 2) * NW) {
+    constexpr int GH = F32_G >= 2 ? F32_G / 2 : 1;
+    if (rem > GH * NW || F32_G == 1) {
       pass(std::integral_constant<int, F32_G>{}, base + vw);
       base += F32_G * NW;
     } else if (rem > NW) {
-      pass(std::integral_constant<int, F32_G / 2>{}, base + vw);
-      base += (F32_G / 2) * NW;
+      pass(std::integral_constant<int, GH>{}, base + vw);
+      base += GH * NW;
     } else {
       pass(std::integral_constant<int, 1>{}, base + vw);
       base += NW;
@@ -295,6 +301,8 @@ __global__ void __launch_bounds__(LD_THREADS, LD_MINB)
     loading_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order,
                        const uint8_t* __restrict__ tile_m, int64_t tile0, int64_t n_det, float* __restrict__ yk,
                        int apply_gain) {
+  extern __shared__ __align__(16) unsigned char dyn[];
+  int4* lks = reinterpret_cast<int4*>(dyn);  // [n_layers][LD_KA] {ix, iy, bits of fx, fy}: the boresight in every layer grid
   __shared__ __align__(16) LayerF ls[MATM_MAX_LAYERS];
   __shared__ float dc_gain[F32_DT];
   __shared__ int dc_band[F32_DT];
@@ -309,6 +317,13 @@ __global__ void __launch_bounds__(LD_THREADS, LD_MINB)
   const int nd = (int)min((int64_t)F32_DT, n_det - dbase);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n_layers = P.n_layers;
+  {
+    const int4* __restrict__ src = reinterpret_cast<const int4*>(P.lk_tab);
+    for (int e = tid; e < n_layers * Wn; e += LD_THREADS) {
+      const int l = e / Wn, k = e % Wn;
+      lks[l * LD_KA + k] = __ldg(src + (size_t)l * n + ka + k);
+    }
+  }
   if (tid < n_layers) {
     const LayerDev& L = P.layers[tid];
     LayerF o;
@@ -320,7 +335,7 @@ __global__ void __launch_bounds__(LD_THREADS, LD_MINB)
     o.ne1 = L.n_ext - 1;
     o.nc1 = L.n_cs - 1;
     o.n_cs = L.n_cs;
-    o.data = reinterpret_cast<const float*>(L.data);
+    o.data2 = reinterpret_cast<const float2*>(L.data2);
     o.pad[0] = o.pad[1] = 0;
     ls[tid] = o;
   }
@@ -342,75 +357,71 @@ __global__ void __launch_bounds__(LD_THREADS, LD_MINB)
   float* yrow = yk + (size_t)tl * n * F32_DT;
   const int tm = nd == F32_DT ? tile_m[dtile] : 1;
   if (tm == 4)
-    loading_tile_f32<4>(P, order, dbase, nd, ka, Wn, n_layers, ls, dc_gain, dc_band, dc_mu, yrow, lane, warp);
+    loading_tile_f32<4>(P, order, dbase, nd, ka, Wn, n_layers, ls, lks, dc_gain, dc_band, dc_mu, yrow, lane, warp);
   else if (tm == 2)
-    loading_tile_f32<2>(P, order, dbase, nd, ka, Wn, n_layers, ls, dc_gain, dc_band, dc_mu, yrow, lane, warp);
+    loading_tile_f32<2>(P, order, dbase, nd, ka, Wn, n_layers, ls, lks, dc_gain, dc_band, dc_mu, yrow, lane, warp);
   else
-    loading_tile_f32<1>(P, order, dbase, nd, ka, Wn, n_layers, ls, dc_gain, dc_band, dc_mu, yrow, lane, warp);
+    loading_tile_f32<1>(P, order, dbase, nd, ka, Wn, n_layers, ls, lks, dc_gain, dc_band, dc_mu, yrow, lane, warp);
 }
 
 // ---------------------------------------------------------------------------------------------------------
 // Kernel B: spline + evaluation + calibration.  One CTA = one tile of 32 slots x F32_KT spline intervals (+ F32_HALO knots
 // of yk on either side for the windowed Thomas sweep).
 //
-// Evaluation (phase 3) is organised for instruction count and for the store path:
-//   * lane = detector PAIR (slots p and p + 16) x half-warp; every arithmetic instruction is a packed f32x2 over the pair.
-//     The spline data of the current interval {y_k, y_k+1 - y_k, M_k, M_k+1} live in registers and are reloaded only when
-//     the interval changes; what depends on the sample only -- the cubic weights a1, a2, a3 (float4 table written once per
-//     scan by sample_weights_kernel) and x = el_b(t) - e_mid -- is one 16-byte record per sample, staged in shared memory
-//     per 128-sample sub-chunk and read as a broadcast LDS.128;
-//   * a thread finishes 4 consecutive samples of its two detectors and puts them into a [32 rows][128 samples] staging
-//     buffer with two conflict-free STS.128; the rows leave through the TMA: one cp.async.bulk.global.shared::cta of up to
-//     512 bytes per row and sub-chunk (L2 evict-first), double-buffered, one CTA barrier per sub-chunk.  No per-sample
-//     address arithmetic, no per-thread global store.
+// Evaluation (phase 3): a thread owns an aligned group of FOUR consecutive full-rate samples and loops over the tile's 32
+// detectors; every arithmetic instruction is a packed f32x2 over two consecutive SAMPLES, the detector's numbers enter as
+// scalar (broadcast) operands, and the four results leave as one 16-byte st.global (a warp writes 512 contiguous bytes of
+// a row).  What depends on the sample only is computed once per group and kept in registers: the cubic weights (a float4
+// table written once per scan by sample_weights_kernel), placed on a THREE-knot stencil so that a group that straddles a
+// knot needs no branch, and x = el_b(t) - e_mid.  Per detector and group the kernel issues 3 LDS.64 (y, M at three knots),
+// 2 loads of constants, 16 packed FMAs, 4 reciprocals and 1 store.
+// The one-kernel version of round 1 spent 2 LDS.128 at ~4 shared-memory wavefronts each per detector pair and SAMPLE and
+// was bound by the L1 data pipe (97 % of peak, ncu); here the shared-memory traffic per sample is ~5x lower.
+//
+// The three-knot stencil needs every interior spline interval to hold at least 4 full-rate samples (checked on the host);
+// coarser scans go through synth_eval_general_f32_kernel (thread = sample, any spacing).
 // ---------------------------------------------------------------------------------------------------------
-#define F32_SUB 128                 // samples per sub-chunk (= row segment handed to the TMA)
-#define F32_RS (F32_SUB + 4)        // staging row stride in floats: 16-byte aligned rows, r * RS mod 32 = 4 r
-__device__ __forceinline__ uint32_t f32_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+struct EvalTile {
+  int k0, k1, wa, wb, Wn, nd, mode;
+  int64_t j0, j1, dbase;
+  double emid;
+};
 
-__global__ void __launch_bounds__(F32_THREADS, F32_MINB)
-    synth_eval_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order, int64_t tile0,
-                          int64_t det0, int64_t n_det, const float* __restrict__ yk, float* __restrict__ out, int units) {
-  extern __shared__ __align__(128) unsigned char dyn[];
-  float4* ym4 = reinterpret_cast<float4*>(dyn);                      // [W][NP] {y_p, y_p+16, m_p, m_p+16}
-  float* ymf = reinterpret_cast<float*>(dyn);
-  float4* splq = ym4 + F32_W * F32_KS;                               // [W] {1/h_k, w_k, a_k w_k, c'_k} (SynthParams::spl)
-  float* stage = reinterpret_cast<float*>(splq + F32_W);             // [2][32][F32_RS]
-  float4* rec = reinterpret_cast<float4*>(stage + 2 * F32_DT * F32_RS);  // [2][F32_SUB] {a1, a2, a3, x}
-  int* rli = reinterpret_cast<int*>(rec + 2 * F32_SUB);              // [2][F32_SUB] local interval of the sample
-  float2* rcs = reinterpret_cast<float2*>(rli + 2 * F32_SUB);        // [2][F32_SUB] {cos, sin}(el_b - pi/2)  (MODE 1 only)
-  __shared__ float dc_u[F32_DT], dc_w[F32_DT];  // rolled offsets: sin el_d = u sin(e) + w cos(e)
-  __shared__ int dc_tab[F32_DT];                // calibration-table base of each detector's band, minus the rounding magic
-  __shared__ int dc_band[F32_DT];
-  __shared__ long long dc_row[F32_DT];          // element offset of each detector's output row
-  __shared__ float dc_p0[F32_DT], dc_p1[F32_DT], dc_p2[F32_DT];  // 1 / factor = P0 + x (P1 + x P2), x = el_b(t) - e_mid
-  __shared__ int s_cal_ie;
-  __shared__ double s_emid;
-
+// Shared prologue of the two evaluation kernels: stage the window of yk, choose the a14 mode of the tile, per-detector
+// constants, spline second derivatives (phase 2).  Shared memory: ym [W][32] {y, M}, splq [W].
+// a14 comes in three flavours, chosen per tile (the choice depends on the time window and on the whole focal plane, not
+// on the detector shard, so shards stay bit-identical): MODE 0 no calibration (pW); MODE 2 the reciprocal of a quadratic
+// in x = el_b(t) - e_mid; MODE 1 the exact evaluation per sample (tiles that cross a point of the elevation grid, or where
+// the quadratic is not accurate enough: near the zenith, or a large change of elevation within the tile).
+__device__ __forceinline__ bool eval_prologue(const SynthParams& P, const int32_t* __restrict__ order, int64_t tile0, int64_t det0,
+                                              int64_t n_det, const float* __restrict__ yk, int units, float2* ym, float4* splq,
+                                              float4* dc_cal, long long* dc_row, float2* dc_uw, int* dc_band, int* s_misc,
+                                              double* s_emid, EvalTile& T) {
   const int n = P.n_t_atm;
   const int n_int = n - 1;
   const int n_ttiles = (n_int + F32_KT - 1) / F32_KT;
   const int64_t tl = blockIdx.x / n_ttiles;
-  const int64_t dtile = tile0 + tl;
   const int ttile = blockIdx.x % n_ttiles;
-  const int k0 = ttile * F32_KT, k1 = min(k0 + F32_KT, n_int);
-  const int wa = max(0, k0 - F32_HALO), wb = min(n - 1, k1 + F32_HALO);
-  const int Wn = wb - wa + 1;
+  T.k0 = ttile * F32_KT;
+  T.k1 = min(T.k0 + F32_KT, n_int);
+  T.wa = max(0, T.k0 - F32_HALO);
+  T.wb = min(n - 1, T.k1 + F32_HALO);
+  T.Wn = T.wb - T.wa + 1;
+  T.dbase = (tile0 + tl) * F32_DT;
+  T.nd = (int)min((int64_t)F32_DT, n_det - T.dbase);
+  T.j0 = P.jstart[T.k0];
+  T.j1 = P.jstart[T.k1];
+  if (T.j0 >= T.j1) return false;  // a time tile that owns no full-rate sample (sample spacing > F32_KT knots)
+  const int k0 = T.k0, k1 = T.k1, wa = T.wa, wb = T.wb, Wn = T.Wn, nd = T.nd;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int64_t dbase = dtile * F32_DT;
-  const int nd = (int)min((int64_t)F32_DT, n_det - dbase);
-  constexpr int MAGIC_BITS = 0x4B400000;  // bits of 1.5 * 2^23
-  const int64_t j0 = P.jstart[k0], j1 = P.jstart[k1];
-  if (j0 >= j1) return;  // a time tile that owns no full-rate sample (sample spacing > F32_KT knots)
   const bool krj = units == MATM_UNITS_KRJ;
+  float* ymf = reinterpret_cast<float*>(ym);
 
   // ---- stage the window: loading at the knots (kernel A's output), spline system, detector constants ----
   {
     const float* __restrict__ src = yk + ((size_t)tl * n + wa) * F32_DT;
-    for (int e = tid; e < Wn * F32_DT; e += F32_THREADS) {
-      const int k = e >> 5, sl = e & 31;
-      ymf[(k * F32_KS + (sl & 15)) * 4 + (sl >> 4)] = __ldcs(src + e);  // read once (plus the halo): streaming
-    }
+    for (int e = tid; e < Wn * F32_DT; e += F32_THREADS)
+      ymf[2 * ((e >> 5) * F32_YS + (e & 31))] = __ldcs(src + e);  // read once (plus the halo): streaming
   }
   if (tid < F32_DT) {
     const int dd = tid;
@@ -418,7 +429,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     int band = 0;
     long long row = 0;
     if (dd < nd) {
-      const int64_t d = order[dbase + dd];  // absolute detector index of this slot
+      const int64_t d = order[T.dbase + dd];  // absolute detector index of this slot
       row = (d - det0) * P.n_t;
       u = (float)P.det_full[2 * d];
       w = (float)P.det_full[2 * d + 1];
@@ -426,17 +437,13 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     }
     dc_band[dd] = band;
     dc_row[dd] = row;
-    dc_u[dd] = u;
-    dc_w[dd] = w;
-    dc_tab[dd] = band * P.calq_n - MAGIC_BITS;
+    dc_uw[dd] = f2(u, w);
   }
   if (warp == F32_THREADS / 32 - 1) {
-    // a14 without a table or a transcendental per sample when (1) every detector stays inside ONE interval of the elevation
-    // grid over the tile's full-rate samples (the usual case: the grid steps are degrees wide), so that H(el) = Hc + Hs el,
-    // and (2) the boresight elevation varies little enough over the tile for the quadratic expansion of el_d(el_b) about
-    // the tile's mid elevation to be exact to 5e-8 rad.  The range is taken over the FULL-RATE samples of the tile
-    // (el_rng), not the knots: turnarounds between knots and the extrapolated tail are covered.  All of it is a property
-    // of the time tile and of the whole focal plane (det_rmax), not of the shard: shards stay bit-identical.
+    // MODE 2 needs (1) every detector inside ONE interval of the elevation grid over the tile's full-rate samples (the
+    // usual case: the grid steps are degrees wide), so that H(el) = Hc + Hs el, and (2) the quadratic expansion of
+    // el_d(el_b) about the tile's mid elevation exact to 5e-8 rad.  The range is taken over the FULL-RATE samples of the
+    // tile (el_rng), not the knots: turnarounds between knots and the extrapolated tail are covered.
     double lo = INFINITY, hi = -INFINITY;
     for (int k = k0 + lane; k < k1; k += 32) {
       lo = fmin(lo, P.el_rng[2 * k]);
@@ -461,8 +468,8 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
         const double rem = 0.5 * r * r * s2 * (2.0 * s2 + 4.0 * t * t) * xmax * xmax * xmax / 6.0;
         if (!(rem <= 5e-8)) ie = -1;
       }
-      s_cal_ie = ie;
-      s_emid = emid;
+      s_misc[0] = ie;
+      *s_emid = emid;
     }
   }
   for (int k = tid; k < Wn; k += F32_THREADS) {
@@ -470,6 +477,9 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     splq[k] = make_float4((float)sp[0], (float)sp[2], (float)sp[3], (float)sp[4]);
   }
   __syncthreads();
+  const int cal_ie = s_misc[0];
+  T.mode = !krj ? 0 : (cal_ie >= 0 ? 2 : 1);
+  T.emid = *s_emid;
   if (tid < F32_DT) {
     // el_d(e) = asin(rho sin(e - beta)) = theta - delta(e), theta = e - beta, rho = 1 - eps; with c = cos el_d:
     //   delta = asin(sin(theta) eps (2 - eps) / (c + rho cos theta))          (no cancellation; asin x = x to 1e-9)
@@ -477,12 +487,12 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
     //   delta'' = -f'' = tan(el_d) (1 - f') (1 + f')
     // H(el_d(e_mid + x)) = Hc + Hs (theta_mid - delta) + Hs (1 - delta') x - Hs delta''/2 x^2 + O(x^3)
     float p0 = 1.f, p1 = 0.f, p2 = 0.f;
-    if (tid < nd && s_cal_ie >= 0) {
-      const int64_t d = order[dbase + tid];
-      const int ho = dc_band[tid] * (P.nel - 1) + s_cal_ie;
+    if (tid < nd && cal_ie >= 0) {
+      const int64_t d = order[T.dbase + tid];
+      const int ho = dc_band[tid] * (P.nel - 1) + cal_ie;
       const double hc = (double)__ldg(reinterpret_cast<const float*>(P.Hc_R) + ho), hs = (double)__ldg(reinterpret_cast<const float*>(P.Hs_R) + ho);
       const double beta = P.det_cal[2 * d], eps = P.det_cal[2 * d + 1];
-      const double th = s_emid - beta, rho = 1.0 - eps;
+      const double th = T.emid - beta, rho = 1.0 - eps;
       double st, ct;
       sincos(th, &st, &ct);
       const double sf = rho * st, c = sqrt(fmax(1.0 - sf * sf, 1e-30));
@@ -492,9 +502,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
       p1 = (float)(hs * (1.0 - d1));
       p2 = (float)(-0.5 * hs * d2);
     }
-    dc_p0[tid] = p0;
-    dc_p1[tid] = p1;
-    dc_p2[tid] = p2;
+    dc_cal[tid] = make_float4(p0, p1, p2, __int_as_float((int)(uint32_t)(dc_row[tid] / P.n_t)));  // .w: output row index
   }
   // ---- phase 2: second derivatives M_k of the not-a-knot cubic spline through the window's knots; lane = detector.
   // Rows of the global tridiagonal system, swept with the global elimination factors.  At a true end of the series the
@@ -503,8 +511,8 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
   // sweeps its own segment of rows plus F32_HALO rows of run-in on either side, so the serial chain is ~40 rows instead
   // of ~300 and no warp idles at the barrier for long.
   {
-    float* row = ymf + (lane & 15) * 4 + (lane >> 4);
-    constexpr int RS = F32_KS * 4;  // stride between knots, in floats
+    float* row = ymf + lane * 2;
+    constexpr int RS = F32_YS * 2;  // stride between knots, in floats
     constexpr int NW = F32_THREADS / 32;
     const int lo = 1, hi = Wn - 2, nrows = hi - lo + 1;
     const int ka = lo + (nrows * warp) / NW, kb = lo + (nrows * (warp + 1)) / NW - 1;  // this warp's rows [ka, kb]
@@ -521,7 +529,7 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
       float4 sp0 = splq[fs - 1], sp1 = splq[fs];
       const float r0 = rhs3(y0, y1, y2, sp0.x, sp1.x);
       float dp = (fs == lo && wa == 0) ? r0 * sp1.y : r0 / (3.f * (1.f / sp0.x + 1.f / sp1.x)) * (1.f + sp1.w);
-      if (fs >= ka) row[fs * RS + 2] = dp;
+      if (fs >= ka) row[fs * RS + 1] = dp;
       for (int k = fs + 1; k <= kb; k++) {
         y0 = y1;
         y1 = y2;
@@ -529,21 +537,21 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
         sp0 = sp1;
         sp1 = splq[k];
         dp = fmaf(rhs3(y0, y1, y2, sp0.x, sp1.x), sp1.y, -sp1.z * dp);
-        if (k >= ka) row[k * RS + 2] = dp;
+        if (k >= ka) row[k * RS + 1] = dp;
       }
     }
     __syncthreads();
     const int be = min(hi, kb + F32_HALO);  // back substitution starts here
     if (ka <= kb) {
 #pragma unroll
-      for (int i = 0; i < F32_HALO; i++) dh[i] = (kb + 1 + i <= be) ? row[(kb + 1 + i) * RS + 2] : 0.f;
+      for (int i = 0; i < F32_HALO; i++) dh[i] = (kb + 1 + i <= be) ? row[(kb + 1 + i) * RS + 1] : 0.f;
     }
     __syncthreads();
     if (ka <= kb) {
       // M just above the segment: exact at the true end of the series, otherwise from the guess one row further up
       float mk;
       if (be == kb) {  // the segment ends at the last row of the window
-        mk = row[kb * RS + 2];
+        mk = row[kb * RS + 1];
         if (wb != n - 1) mk -= splq[kb].w * guess_at(kb);
       } else {
         mk = 0.f;
@@ -556,167 +564,187 @@ __global__ void __launch_bounds__(F32_THREADS, F32_MINB)
           else if (k < be)
             mk = fmaf(-splq[k].w, mk, dh[i]);
         }
-        mk = fmaf(-splq[kb].w, mk, row[kb * RS + 2]);
+        mk = fmaf(-splq[kb].w, mk, row[kb * RS + 1]);
       }
-      row[kb * RS + 2] = mk;
+      row[kb * RS + 1] = mk;
       for (int k = kb - 1; k >= ka; k--) {
-        mk = fmaf(-splq[k].w, mk, row[k * RS + 2]);
-        row[k * RS + 2] = mk;
+        mk = fmaf(-splq[k].w, mk, row[k * RS + 1]);
+        row[k * RS + 1] = mk;
       }
     }
     __syncthreads();
     if (warp == 0) {
-      const float m1 = row[RS + 2], m2 = row[2 * RS + 2];
-      row[2] = (wa == 0) ? m1 - (splq[1].x / splq[0].x) * (m2 - m1) : m1;
+      const float m1 = row[RS + 1], m2 = row[2 * RS + 1];
+      row[1] = (wa == 0) ? m1 - (splq[1].x / splq[0].x) * (m2 - m1) : m1;
     } else if (warp == 1) {
-      const float me = row[(Wn - 2) * RS + 2], me2 = row[(Wn - 3) * RS + 2];
-      row[(Wn - 1) * RS + 2] = (wb == n - 1) ? me + (splq[Wn - 3].x / splq[Wn - 2].x) * (me - me2) : me;
+      const float me = row[(Wn - 2) * RS + 1], me2 = row[(Wn - 3) * RS + 1];
+      row[(Wn - 1) * RS + 1] = (wb == n - 1) ? me + (splq[Wn - 3].x / splq[Wn - 2].x) * (me - me2) : me;
     }
   }
   __syncthreads();
 
-  // ---- phase 3: evaluate at the full-rate samples of the tile (see the header of this kernel) ----
-  const int p = lane & 15, hw = lane >> 4;
-  const int mode = !krj ? 0 : (s_cal_ie >= 0 ? 2 : 1);
-  const double emid = s_emid;
-  const int64_t J0 = j0 & ~(int64_t)(F32_SUB - 1);
-  const int n_sub = (int)((j1 - J0 + F32_SUB - 1) / F32_SUB);
-  const float2* __restrict__ calq = P.calq;
-  // the rows can go through the TMA when every row segment is 16-byte aligned in global memory (the sub-chunk grid is
-  // aligned to 128 samples, so shared and global phases agree); otherwise all threads store scalars
-  const bool bulk_ok = (P.n_t % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-  uint64_t pol = 0;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  // per-pair constants, in registers for the whole tile
-  const float2 P0 = f2(dc_p0[p], dc_p0[p + 16]), P1 = f2(dc_p1[p], dc_p1[p + 16]), P2 = f2(dc_p2[p], dc_p2[p + 16]);
-  const float2 U2 = f2(dc_u[p], dc_u[p + 16]), W2 = f2(dc_w[p], dc_w[p + 16]);
-  const int tb0 = dc_tab[p], tb1 = dc_tab[p + 16], bd0 = dc_band[p], bd1 = dc_band[p + 16];
-
-  // one 16-byte record per sample of a sub-chunk: the cubic weights and x (MODE 2) or the boresight (MODE 1)
-  auto make_records = [&](int c, int buf) {
-    if (tid < F32_SUB) {
-      const int64_t j = max(min(J0 + (int64_t)c * F32_SUB + tid, j1 - 1), j0);  // outside the tile: repeat its edge sample
-      const float4 w = __ldg(P.samp_w + j);  // {a1, a2, a3, interval}
-      float x = 0.f;
-      if (mode == 2) x = (float)(P.el_full[j] - emid);
-      rec[buf * F32_SUB + tid] = make_float4(w.x, w.y, w.z, x);
-      rli[buf * F32_SUB + tid] = min(max(__float_as_int(w.w), k0), k1 - 1) - wa;
-      if (mode == 1) {
-        const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
-        rcs[buf * F32_SUB + tid] = f2((float)bf.x, (float)bf.y);
-      }
-    }
-  };
-  make_records(0, 0);
   __syncthreads();
+  return true;
+}
 
-  int cur = -1;
-  float2 y0 = f2(0.f, 0.f), dy = y0, m0 = y0, m1 = y0;
-  auto reload = [&](int li) {
-    const float4 q0 = ym4[li * F32_KS + p], q1 = ym4[(li + 1) * F32_KS + p];
-    y0 = f2(q0.x, q0.y);
-    dy = __fadd2_rn(f2(q1.x, q1.y), f2(-q0.x, -q0.y));
-    m0 = f2(q0.z, q0.w);
-    m1 = f2(q1.z, q1.w);
-    cur = li;
-  };
-  auto eval = [&](auto mode_tag, const float4 r, const float2 cs) -> float2 {
-    constexpr int MODE = decltype(mode_tag)::value;
-    float2 v = __ffma2_rn(f2(r.x, r.x), dy, y0);
-    v = __ffma2_rn(f2(r.y, r.y), m0, v);
-    v = __ffma2_rn(f2(r.z, r.z), m1, v);
-    if constexpr (MODE == 2) {
-      const float2 x2 = f2(r.w, r.w);
-      float2 den = __ffma2_rn(P2, x2, P1);
-      den = __ffma2_rn(den, x2, P0);
-      v = __fmul2_rn(v, f2(fast_rcp(den.x), fast_rcp(den.y)));
-    } else if constexpr (MODE == 1) {
-      const float2 sn = __ffma2_rn(U2, f2(cs.y, cs.y), __fmul2_rn(W2, f2(cs.x, cs.x)));
-      // |1 - sin el|: sin el can exceed 1 by an ulp; inputs are finite (checked by matm_set_scan / matm_set_detectors)
-      const float2 t = f2(fast_sqrt(fabsf(1.f - sn.x)), fast_sqrt(fabsf(1.f - sn.y)));
-      const float2 x = __ffma2_rn(t, f2(MATM_CAL_SCALE, MATM_CAL_SCALE), f2(12582912.f, 12582912.f));  // round(t * scale) in the low mantissa bits
-      const float2 rr = __fadd2_rn(x, f2(-12582912.f, -12582912.f));
-      const float2 dt = __ffma2_rn(t, f2(MATM_CAL_SCALE, MATM_CAL_SCALE), f2(-rr.x, -rr.y));
-      const int i0 = __float_as_int(x.x) + tb0, i1 = __float_as_int(x.y) + tb1;
-      const float2 c0 = __ldg(calq + i0), c1 = __ldg(calq + i1);
-      float2 f = f2(fmaf(c0.y, dt.x, c0.x), fmaf(c1.y, dt.y, c1.x));
-      if (!(f.x * f.y == f.x * f.y)) {  // a bin with a grid point of the elevation table, or outside the table
-        if (!(f.x == f.x)) f.x = cal_factor_special(P, i0, bd0, sn.x, dt.x);
-        if (!(f.y == f.y)) f.y = cal_factor_special(P, i1, bd1, sn.y, dt.y);
-      }
-      v = __fmul2_rn(v, f);
-    }
-    return v;
-  };
+// exact a14 factor of one detector sample (MODE 1): the generic searching code of matm_synth.cuh
+__device__ __forceinline__ float cal_exact_f32(const SynthParams& P, int band, float u, float w, float ce, float se, int& ie) {
+  const int ho = band * (P.nel - 1);
+  const float den = cal_denominator<float>(P, reinterpret_cast<const float*>(P.sinel_R), reinterpret_cast<const float*>(P.Hc_R) + ho,
+                                           reinterpret_cast<const float*>(P.Hs_R) + ho, fmaf(u, se, w * ce), ie);
+  return 1.0f / den;
+}
 
+__global__ void __launch_bounds__(F32_THREADS, F32_MINB)
+    synth_eval_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order, int64_t tile0,
+                          int64_t det0, int64_t n_det, const float* __restrict__ yk, float* __restrict__ out, int units) {
+  extern __shared__ __align__(16) unsigned char dyn[];
+  float2* ym = reinterpret_cast<float2*>(dyn);                                // [W][32] {y, M}
+  float4* splq = reinterpret_cast<float4*>(ym + (size_t)F32_W * F32_YS);      // [W] {1/h_k, w_k, a_k w_k, c'_k}
+  __shared__ float4 dc_cal[F32_DT];                 // {P0, P1, P2, -}: 1 / factor = P0 + x (P1 + x P2)
+  __shared__ __align__(16) long long dc_row[F32_DT];  // element offset of each detector's output row
+  __shared__ float2 dc_uw[F32_DT];                  // rolled offsets: sin el_d = u sin(e) + w cos(e)
+  __shared__ int dc_band[F32_DT];
+  __shared__ int s_misc[2];
+  __shared__ double s_emid;
+  EvalTile T;
+  if (!eval_prologue(P, order, tile0, det0, n_det, yk, units, ym, splq, dc_cal, dc_row, dc_uw, dc_band, s_misc, &s_emid, T)) return;
+
+  const int tid = threadIdx.x;
+  const int64_t j0 = T.j0, j1 = T.j1;
+  const int nd = T.nd, wa = T.wa;
+  const bool vec_ok = (P.n_t % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  const uint32_t n_t32 = (uint32_t)P.n_t * 4u;  // bytes per output row
   auto phase3 = [&](auto mode_tag) {
     constexpr int MODE = decltype(mode_tag)::value;
-    for (int c = 0; c < n_sub; c++) {
-      const int buf = c & 1;
-      if (c + 1 < n_sub) make_records(c + 1, buf ^ 1);
-      const float4* __restrict__ rc = rec + buf * F32_SUB;
-      const int* __restrict__ rl = rli + buf * F32_SUB;
-      const float2* __restrict__ rs = rcs + buf * F32_SUB;
-      float* __restrict__ sg = stage + buf * (F32_DT * F32_RS);
+    for (int64_t jb = (j0 & ~(int64_t)3) + 4 * (int64_t)tid; jb < j1; jb += 4 * F32_THREADS) {
+      // the group's samples; those outside the tile (first / last group) repeat the nearest owned one and are not stored
+      float2 W0[2], W1[2], W2[2], U0[2], U1[2], U2[2], X[2];
+      int kb = 0;
 #pragma unroll
-      for (int g = 0; g < F32_SUB / 64; g++) {
-        const int col = (F32_SUB / 8) * warp + (F32_SUB / 16) * hw + 4 * g;
-        const int4 li4 = *reinterpret_cast<const int4*>(rl + col);
-        float2 v[4];
-        if (li4.x == li4.w) {  // the four samples lie in one spline interval (the usual case)
-          if (li4.x != cur) reload(li4.x);
+      for (int q = 0; q < 4; q++) {
+        const int64_t j = max(min(jb + q, j1 - 1), j0);
+        const float4 w = __ldg(P.samp_w + j);  // {a1, a2, a3, interval}
+        const int li = min(max(__float_as_int(w.w), T.k0), T.k1 - 1) - wa;
+        if (q == 0) kb = li;
+        const bool up = li != kb;  // the sample lies one interval further (at most one knot inside a group)
+        const float a0 = 1.f - w.x;
+        float* f;
+        f = reinterpret_cast<float*>(W0) + q, *f = up ? 0.f : a0;
+        f = reinterpret_cast<float*>(W1) + q, *f = up ? a0 : w.x;
+        f = reinterpret_cast<float*>(W2) + q, *f = up ? w.x : 0.f;
+        f = reinterpret_cast<float*>(U0) + q, *f = up ? 0.f : w.y;
+        f = reinterpret_cast<float*>(U1) + q, *f = up ? w.y : w.z;
+        f = reinterpret_cast<float*>(U2) + q, *f = up ? w.z : 0.f;
+        if constexpr (MODE == 2) reinterpret_cast<float*>(X)[q] = (float)(P.el_full[j] - T.emid);
+      }
+      const float2* __restrict__ yb = ym + kb * F32_YS;
+      // the third knot of the stencil: a group in the last interval of the window never looks further (its weights there
+      // are zero, the address just has to be valid)
+      const int o2 = (kb + 2 <= T.Wn - 1) ? 2 * F32_YS : F32_YS;
+      const bool full = vec_ok && jb >= j0 && jb + 4 <= j1;
+      const char* const obase = reinterpret_cast<const char*>(out + jb);
+      int ie = 0;  // interval of the elevation grid found last (MODE 1)
+      auto detectors = [&](auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
+        constexpr int UNR = F32_UNROLL;
+#pragma unroll UNR
+        for (int d = 0; d < nd; d++) {
+          const float2 q0 = yb[d], q1 = yb[F32_YS + d], q2 = yb[o2 + d];
+          const float4 c = dc_cal[d];  // {P0, P1, P2, bits of the output row index}
+          float2 v[2];
 #pragma unroll
-          for (int q = 0; q < 4; q++) v[q] = eval(mode_tag, rc[col + q], MODE == 1 ? rs[col + q] : f2(0.f, 0.f));
-        } else {
-          const int li[4] = {li4.x, li4.y, li4.z, li4.w};
+          for (int h = 0; h < 2; h++) {
+            float2 t = __fmul2_rn(W0[h], f2(q0.x, q0.x));
+            t = __ffma2_rn(W1[h], f2(q1.x, q1.x), t);
+            t = __ffma2_rn(W2[h], f2(q2.x, q2.x), t);
+            t = __ffma2_rn(U0[h], f2(q0.y, q0.y), t);
+            t = __ffma2_rn(U1[h], f2(q1.y, q1.y), t);
+            v[h] = __ffma2_rn(U2[h], f2(q2.y, q2.y), t);
+          }
+          if constexpr (MODE == 2) {
 #pragma unroll
-          for (int q = 0; q < 4; q++) {
-            if (li[q] != cur) reload(li[q]);
-            v[q] = eval(mode_tag, rc[col + q], MODE == 1 ? rs[col + q] : f2(0.f, 0.f));
+            for (int h = 0; h < 2; h++) {
+              float2 den = __ffma2_rn(X[h], f2(c.z, c.z), f2(c.y, c.y));
+              den = __ffma2_rn(den, X[h], f2(c.x, c.x));
+              v[h] = __fmul2_rn(v[h], f2(fast_rcp(den.x), fast_rcp(den.y)));
+            }
+          } else if constexpr (MODE == 1) {
+            const float2 uw = dc_uw[d];
+            const int band = dc_band[d];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              const int64_t j = max(min(jb + q, j1 - 1), j0);
+              const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
+              reinterpret_cast<float*>(v)[q] *= cal_exact_f32(P, band, uw.x, uw.y, (float)bf.x, (float)bf.y, ie);
+            }
+          }
+          // row offset = row index x row bytes: one 32 x 32 + 64 -> 64-bit multiply-add (n_t < 2^30 on this path)
+          float* o = reinterpret_cast<float*>(const_cast<char*>(obase) + (uint64_t)(uint32_t)__float_as_int(c.w) * (uint64_t)n_t32);
+          if constexpr (FULL) {
+            __stcs(reinterpret_cast<float4*>(o), make_float4(v[0].x, v[0].y, v[1].x, v[1].y));
+          } else {
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+              if (jb + q >= j0 && jb + q < j1) __stcs(o + q, reinterpret_cast<const float*>(v)[q]);
           }
         }
-        *reinterpret_cast<float4*>(sg + p * F32_RS + col) = make_float4(v[0].x, v[1].x, v[2].x, v[3].x);
-        *reinterpret_cast<float4*>(sg + (p + 16) * F32_RS + col) = make_float4(v[0].y, v[1].y, v[2].y, v[3].y);
-      }
-      // hand the sub-chunk to the TMA: writes visible to the async proxy, the other buffer's previous read finished
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      if (tid < F32_DT) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-      __syncthreads();
-      const int64_t J = J0 + (int64_t)c * F32_SUB;
-      const int64_t ja = max(J, j0), jb = min(J + F32_SUB, j1);
-      if (bulk_ok) {
-        if (tid < nd) {
-          float* dst = out + dc_row[tid];
-          const float* src = sg + tid * F32_RS;
-          const int64_t ja4 = (ja + 3) & ~(int64_t)3, jb4 = jb & ~(int64_t)3;
-          if (ja4 < jb4) {
-            asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst + ja4),
-                         "r"(f32_smem_u32(src + (ja4 - J))), "r"((uint32_t)(jb4 - ja4) * 4u), "l"(pol)
-                         : "memory");
-          }
-          for (int64_t j = ja; j < min(ja4, jb); j++) __stcs(dst + j, src[j - J]);
-          for (int64_t j = max(jb4, ja4); j < jb; j++) __stcs(dst + j, src[j - J]);
-        }
-        if (tid < F32_DT) asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      } else {
-        const int len = (int)(jb - ja);
-        for (int e = tid; e < nd * len; e += F32_THREADS) {
-          const int r = e / len, jj = e % len;
-          __stcs(out + dc_row[r] + ja + jj, sg[r * F32_RS + (int)(ja - J) + jj]);
-        }
-      }
+      };
+      if (full)
+        detectors(std::true_type{});
+      else
+        detectors(std::false_type{});
     }
-    if (tid < F32_DT) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // shared memory must outlive the reads
   };
-  if (mode == 0)
+  if (T.mode == 0)
     phase3(std::integral_constant<int, 0>{});
-  else if (mode == 2)
+  else if (T.mode == 2)
     phase3(std::integral_constant<int, 2>{});
   else
     phase3(std::integral_constant<int, 1>{});
 }
 
-static size_t synth_f32_smem() {
-  return (size_t)F32_W * F32_KS * sizeof(float4) + (size_t)F32_W * sizeof(float4) + 2 * F32_DT * F32_RS * sizeof(float) +
-         2 * F32_SUB * (sizeof(float4) + sizeof(int) + sizeof(float2));
+// Any sample spacing (fewer than four full-rate samples per spline interval): thread = sample, loop over the detectors.
+__global__ void __launch_bounds__(F32_THREADS)
+    synth_eval_general_f32_kernel(const __grid_constant__ SynthParams P, const int32_t* __restrict__ order, int64_t tile0,
+                                  int64_t det0, int64_t n_det, const float* __restrict__ yk, float* __restrict__ out, int units) {
+  extern __shared__ __align__(16) unsigned char dyn[];
+  float2* ym = reinterpret_cast<float2*>(dyn);
+  float4* splq = reinterpret_cast<float4*>(ym + (size_t)F32_W * F32_YS);
+  __shared__ float4 dc_cal[F32_DT];
+  __shared__ __align__(16) long long dc_row[F32_DT];
+  __shared__ float2 dc_uw[F32_DT];
+  __shared__ int dc_band[F32_DT];
+  __shared__ int s_misc[2];
+  __shared__ double s_emid;
+  EvalTile T;
+  if (!eval_prologue(P, order, tile0, det0, n_det, yk, units, ym, splq, dc_cal, dc_row, dc_uw, dc_band, s_misc, &s_emid, T)) return;
+  for (int64_t j = T.j0 + threadIdx.x; j < T.j1; j += F32_THREADS) {
+    const float4 w = __ldg(P.samp_w + j);
+    const int li = min(max(__float_as_int(w.w), T.k0), T.k1 - 1) - T.wa;
+    const float a0 = 1.f - w.x;
+    const float x = T.mode == 2 ? (float)(P.el_full[j] - T.emid) : 0.f;
+    float ce = 0.f, se = 0.f;
+    if (T.mode == 1) {
+      const double2 bf = *reinterpret_cast<const double2*>(P.bore_full + 2 * j);
+      ce = (float)bf.x;
+      se = (float)bf.y;
+    }
+    const float2* __restrict__ yb = ym + li * F32_YS;
+    int ie = 0;
+    for (int d = 0; d < T.nd; d++) {
+      const float2 q0 = yb[d], q1 = yb[F32_YS + d];
+      float v = fmaf(w.z, q1.y, fmaf(w.y, q0.y, fmaf(w.x, q1.x, a0 * q0.x)));
+      if (T.mode == 2) {
+        const float4 c = dc_cal[d];
+        v *= fast_rcp(fmaf(fmaf(c.z, x, c.y), x, c.x));
+      } else if (T.mode == 1) {
+        const float2 uw = dc_uw[d];
+        v *= cal_exact_f32(P, dc_band[d], uw.x, uw.y, ce, se, ie);
+      }
+      __stcs(out + dc_row[d] + j, v);
+    }
+  }
 }
+
+static size_t synth_f32_smem() { return (size_t)F32_W * F32_YS * sizeof(float2) + (size_t)F32_W * sizeof(float4); }

@@ -7,20 +7,21 @@ noise, and the detector x time stages against the oracle fed with the device's o
 spread over the whole focal plane.  Size-independent properties (gain linearity, unit round trip, shard bit-equality,
 determinism) are checked on the device at C4 geometry.
 
-Tolerances: fp64 path 1e-10 relative; fp32 path 2e-6 on the total TOD and 5e-4 on its fluctuating part.
+Tolerances: fp64 path 1e-10 relative; fp32 path 2e-6 on the total TOD (4e-6 on the samples extrapolated beyond the last
+knot) and 5e-4 on its fluctuating part -- stated in tests/common.py.
 """
 import numpy as np
 import pytest
 
 import maria_b200 as M
-from common import relmax
+from common import check32, relmax
 from maria_b200 import configs
 from maria_b200 import inputs as I
 from oracle import atm_oracle as O
 
 pytestmark = pytest.mark.gpu
 
-TOL64, TOL32_TOTAL, TOL32_FLUCT = 1e-10, 2e-6, 5e-4
+TOL64 = 1e-10
 
 
 def _device(cfg, dtype, np_seed, **akw):
@@ -36,11 +37,12 @@ def _oracle(cfg, seed):
                       dtype=np.float64)
 
 
-def _check32(dev, ref):
-    assert relmax(dev, ref) < TOL32_TOTAL
-    mean = ref.mean(axis=1, keepdims=True)
-    fl_ref, fl_dev = ref - mean, np.asarray(dev, dtype=np.float64) - mean
-    assert np.max(np.abs(fl_dev - fl_ref)) / np.max(np.abs(fl_ref)) < TOL32_FLUCT
+def _check32(dev, ref, sim=None):
+    """common.check32 with the knot range of the simulation's atmosphere-rate axis (None: every sample counts as inside)."""
+    if sim is None:
+        return check32(dev, ref)
+    obs = sim.obs_list[0]
+    check32(dev, ref, obs.boresight.t, obs.atmosphere.boresight.t[-1])
 
 
 @pytest.mark.parametrize("name, kwargs", [
@@ -54,9 +56,10 @@ def test_baseline_config_matches_oracle(cuda, name, kwargs):
     ref = _oracle(cfg, seed=17)["tod_K_RJ"]
     tod64 = _device(cfg, np.float64, 17, geometry="exact").run(units="K_RJ")[0].data["atmosphere"]
     assert tod64.shape == ref.shape and relmax(tod64, ref) < TOL64
-    tod32 = _device(cfg, np.float32, 17, geometry="exact").run(units="K_RJ")[0].data["atmosphere"]
+    sim32 = _device(cfg, np.float32, 17, geometry="exact")
+    tod32 = sim32.run(units="K_RJ")[0].data["atmosphere"]
     assert tod32.dtype == np.float32
-    _check32(tod32, ref)
+    _check32(tod32, ref, sim32)
 
 
 # ---- C4 geometry: full time axis, full-size layers ---------------------------------------------------------------
@@ -127,7 +130,7 @@ def test_c4_full_time_axis_matches_oracle(cuda, c4):
             ref = _oracle_with_layers(c4, atm, sel, layers)
     assert out[np.float64].shape == ref.shape == (len(sel), 180000)
     assert relmax(out[np.float64], ref) < TOL64
-    _check32(out[np.float32], ref)
+    _check32(out[np.float32], ref, sim)
 
 
 def test_c4_properties_on_device(cuda, c4):
@@ -168,7 +171,7 @@ def test_colocated_detectors_share_the_line_of_sight_bit_exactly(cuda):
     assert np.array_equal(dets.offsets[:256], dets.offsets[256:512]) and dets.band_name[0] != dets.band_name[256]
     sim = _device(cfg, np.float32, 29, geometry="exact")
     full = sim.run(units="K_RJ")[0].data["atmosphere"]
-    _check32(full, _oracle(cfg, seed=29)["tod_K_RJ"])
+    _check32(full, _oracle(cfg, seed=29)["tod_K_RJ"], sim)
     obs = sim.obs_list[0]
     shard = sim._compute_atmospheric_loading(obs, 512, 512, units="K_RJ", apply_gain=True).cpu().numpy()    # rank 1 of 2: paired
     unpaired = sim._compute_atmospheric_loading(obs, 513, 511, units="K_RJ", apply_gain=True).cpu().numpy()
@@ -225,7 +228,7 @@ def test_c5_six_hour_scan_runs_and_matches_oracle_subset(cuda):
     assert tod.shape == (n, 1080000) and bool(cuda.isfinite(tod).all())
     sel = np.array([0, n // 3, n - 1])
     ref = _oracle_with_layers(cfg, atm, sel, {k: p.values for k, p in atm.processes.items()})
-    _check32(tod[sel].cpu().numpy(), ref)
+    _check32(tod[sel].cpu().numpy(), ref, sim)
 
 
 def _log_binned_psd(x, rate, n_bins=12):

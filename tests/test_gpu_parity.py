@@ -3,21 +3,20 @@ oracle/pin_against_reference.py from the unmodified reference) and against the o
 
 Tolerances (stated here, used below):
   fp64 path vs reference / oracle, identical host noise ........ 1e-10 relative (max |diff| / max |ref|)
-  fp32 path vs the float64 oracle ............................... 2e-6 relative on the total TOD,
-                                                                  5e-4 relative on its fluctuating part
+  fp32 path vs the float64 oracle ............................... 2e-6 relative on the total TOD (4e-6 on the samples
+                                                                  extrapolated beyond the last knot), 5e-4 relative on
+                                                                  its fluctuating part (tests/common.py: check32)
 """
 import numpy as np
 import pytest
 
 import maria_b200 as M
-from common import load_case, relmax, small_case
+from common import check32, load_case, relmax, small_case
 from oracle import atm_oracle as O
 
 pytestmark = pytest.mark.gpu
 
 TOL64 = 1e-10
-TOL32_TOTAL = 2e-6
-TOL32_FLUCT = 5e-4
 
 
 def run_device(case, dtype, units="K_RJ", **akw):
@@ -64,11 +63,8 @@ def test_fp32_within_stated_bound_of_reference(cuda, name):
     krj = tod.data["atmosphere"]
     assert krj.dtype == np.float32
     sel = fx["det_sel"]
-    ref = fx["ref_tod_K_RJ_sel"]
-    assert relmax(krj[sel], ref) < TOL32_TOTAL
-    fl_ref = ref - ref.mean(axis=1, keepdims=True)
-    fl_dev = krj[sel].astype(np.float64) - ref.mean(axis=1, keepdims=True)
-    assert np.max(np.abs(fl_dev - fl_ref)) / np.max(np.abs(fl_ref)) < TOL32_FLUCT
+    obs = sim.obs_list[0]
+    check32(krj[sel], fx["ref_tod_K_RJ_sel"], obs.boresight.t, obs.atmosphere.boresight.t[-1])
 
 
 def test_stages_against_oracle_fresh_inputs(cuda):
