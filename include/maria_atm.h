@@ -36,7 +36,7 @@ enum {
 enum { MATM_F32 = 0, MATM_F64 = 1 };           /* arithmetic + storage type of layers / TOD */
 enum { MATM_UNITS_PW = 0, MATM_UNITS_KRJ = 1 }; /* TOD units (tod.py:106-142) */
 
-#define MATM_MAX_LAYERS 16
+#define MATM_MAX_LAYERS 64  /* the "3d" model has one layer per resolution element of height (extrusion.py:69-77) */
 #define MATM_MAX_BANDS 16
 
 /* One turbulent layer as the sampler sees it (atmosphere.py:317-373). */

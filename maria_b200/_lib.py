@@ -12,7 +12,7 @@ from . import _build
 OK, ERR_CUDA, ERR_ARG, ERR_OUT_OF_GRID, ERR_TABLE_RANGE = 0, 1, 2, 3, 4
 F32, F64 = 0, 1
 UNITS_PW, UNITS_KRJ = 0, 1
-MAX_LAYERS, MAX_BANDS = 16, 16
+MAX_LAYERS, MAX_BANDS = 64, 16
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)

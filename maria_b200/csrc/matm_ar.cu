@@ -2,14 +2,17 @@
 //
 //   BUFFER[i] = A @ BUFFER[i + 1 + esi, csi] + B @ z_i      for i = 2 n_ext - 1 ... 0
 //
-// Two kernels.  (1) bz_gemm_kernel: the only genuinely dense contraction, B @ z for ALL steps at once
-// (M = 2 n_ext, N = K = n_cs), written straight into BUFFER rows [0, 2 n_ext).  (2) ar_chain_kernel: the
-// sequential recurrence.  One thread-block cluster per process; every CTA keeps its slice of rows of A resident
-// in shared memory (staged once with the TMA bulk-copy engine) for all 2 n_ext steps, the gather vector is
-// rebuilt from the L2-resident BUFFER each step and the CTAs of the cluster meet at a hardware cluster barrier.
+// Three kernels.  (1) bz_gemm_kernel: the only genuinely dense contraction, B @ z for ALL steps at once
+// (M = 2 n_ext, N = K = n_cs), written straight into BUFFER rows [0, 2 n_ext).  (2) ar_chain_v4_kernel: the sequential
+// recurrence of every process that fits it (all "2d" processes: n_sample <= 1280, n_cs <= 8 x 128): one thread-block
+// cluster per process, A in REGISTERS (L lanes per row), the gather vectors in shared memory, every produced value sent
+// with st.async into the gather vectors of the next three steps of every CTA of the cluster, completing bytes on mbarriers
+// of the destination CTA -- no cluster barrier, no fence on the critical path.  (3) ar_chain_kernel: the general
+// recurrence for larger processes (the coupled "3d" model: n_cs and n_sample in the thousands): every CTA of the cluster
+// keeps its slice of rows of A in shared memory when it fits (staged once with the TMA bulk-copy engine), else streams
+// it from L2; the gather vector is rebuilt from the L2-resident BUFFER each step and the CTAs meet at a hardware cluster
+// barrier.  Both chain kernels are covered by parity tests (tests/test_gpu_parity.py, tests/test_gpu_configs.py).
 #include <cooperative_groups.h>
-#include <stdlib.h>
-
 #include <type_traits>
 
 #include "matm_common.cuh"
@@ -187,167 +190,20 @@ static int launch_chain(matm_handle* h, const double* A, const int* esi, const i
   return MATM_OK;
 }
 
-// ---------------------------------------------------------------------------------------------------------
-// The chain, latency-optimised (v3).  A step is bounded by the round trips on its critical path, not by arithmetic,
-// so everything that is not "the previous row" is taken off that path and the rest is made short:
-//   * A lives in REGISTERS.  L lanes share a row (32 / L rows per warp): lane `sub` holds the entries of samples
-//     sub, sub + L, ...  ->  the cross-lane reduction is log2(L) shuffle stages instead of 5 per row;
-//   * the gather vector of step i is a contiguous shared-memory array G[i & 3][n_sample]: whoever produces a value
-//     writes it straight to where its consumers will read it -- the owner of (row i, column c) stores it into the
-//     G arrays of steps i-1, i-2, i-3 (stencil offsets 1..3) of EVERY CTA of the cluster through distributed
-//     shared memory, and the stencil rows further back (offsets >= 4) plus the row's own B z term are fetched
-//     from L2 two / three steps ahead of their use through a register pipeline, so their latency never shows;
-//   * one barrier per step: __syncthreads (1 CTA) or the hardware cluster barrier.
-// ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void cluster_barrier() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
 }
-__device__ __forceinline__ void st_dsmem_f64(double* local_ptr, int cta, double v) {
-  uint32_t a = smem_u32(local_ptr), r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(cta));
-  asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(r), "d"(v) : "memory");
-}
-
-template <int L, int MP>
-__global__ void __launch_bounds__(AR_THREADS, 1)
-    ar_chain_v3_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
-                       double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl) {
-  constexpr int RPW = 32 / L;  // rows per warp
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int gs = L * MP;                                  // padded length of one gather vector
-  double* G = reinterpret_cast<double*>(smem_raw);        // [4][gs]
-  int* pos = reinterpret_cast<int*>(G + 4 * (size_t)gs);  // [3][n_cs]: position of column c among the samples of offset 1, 2, 3
-  const int n_far = n_sample - n_near;
-  int cta = 0;
-  if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
-  const int rpc = (n_cs + cl - 1) / cl;
-  const int row0 = cta * rpc;
-  const int rows = max(0, min(n_cs, row0 + rpc) - row0);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int rr = lane / L, sub = lane % L;
-  const int r = warp * RPW + rr;  // row within this CTA
-  const bool has_row = r < rows;
-  const int i_top = 2 * n_ext - 1;
-
-  // ---- set-up: A into registers, G zeroed, inverse stencil maps ----
-  double a[MP];
-#pragma unroll
-  for (int m = 0; m < MP; m++) {
-    const int s = sub + L * m;
-    a[m] = (has_row && s < n_sample) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
-  }
-  for (int e = tid; e < 4 * gs; e += AR_THREADS) G[e] = 0.0;
-  for (int e = tid; e < 3 * n_cs; e += AR_THREADS) pos[e] = -1;
-  __syncthreads();
-  for (int s = tid; s < n_near; s += AR_THREADS) pos[esi[s] * n_cs + csi[s]] = s;  // offset = esi + 1 in 1..3
-  // far sample f is fetched by thread f (n_far <= 2 * AR_THREADS): global offset relative to the row being computed
-  int foff[2];
-#pragma unroll
-  for (int q = 0; q < 2; q++) {
-    const int f = tid + q * AR_THREADS;
-    foff[q] = f < n_far ? (esi[n_near + f] + 1) * n_cs + csi[n_near + f] : -1;
-  }
-  __syncthreads();
-  // where this thread's row goes in the gather vectors of the next three steps (publisher lanes only)
-  int p1 = -1, p2 = -1, p3 = -1;
-  if (has_row && sub == 0) {
-    p1 = pos[row0 + r];
-    p2 = pos[n_cs + row0 + r];
-    p3 = pos[2 * n_cs + row0 + r];
-  }
-  // ---- prologue: the initial-noise rows i_top+1 .. i_top+3 feed steps i_top, i_top-1, i_top-2 ----
-  for (int e = tid; e < 3 * n_near; e += AR_THREADS) {
-    const int k = e / n_near, s = e % n_near;  // step i_top - k, near sample s
-    const int off = esi[s] + 1;
-    if (off > k && i_top - k >= 0)
-      G[((i_top - k) & 3) * gs + s] = buffer[(size_t)(i_top - k + off) * n_cs + csi[s]];
-  }
-#pragma unroll
-  for (int q = 0; q < 2; q++)
-    if (foff[q] >= 0) {
-      const int f = n_near + tid + q * AR_THREADS;
-      G[(i_top & 3) * gs + f] = buffer[(size_t)i_top * n_cs + foff[q]];
-      if (i_top >= 1) G[((i_top - 1) & 3) * gs + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
-    }
-  // Register pipelines, two sets each, used alternately by even / odd steps so that no register is copied while its
-  // load is still in flight (the loop below is unrolled by two for that reason):
-  //   far_s[i & 1]: issued at step i + 2 for step i - 1, landed in G at the start of step i, then re-issued
-  //   bz_s[i & 1] : issued at step i + 2 for step i, consumed when step i publishes, then re-issued for step i - 2
-  double far_s[2][2], bz_s[2];
-  far_s[0][0] = far_s[0][1] = far_s[1][0] = far_s[1][1] = 0.0;
-  bz_s[0] = bz_s[1] = 0.0;
-  if (has_row) {  // i_top is odd: set 1 serves step i_top, set 0 step i_top - 1
-    bz_s[1] = buffer[(size_t)i_top * n_cs + row0 + r];
-    bz_s[0] = buffer[(size_t)(i_top - 1) * n_cs + row0 + r];
-  }
-#pragma unroll
-  for (int q = 0; q < 2; q++)  // far values of step i_top - 2 are landed by step i_top - 1 (set 0)
-    if (foff[q] >= 0 && i_top >= 2) far_s[0][q] = buffer[(size_t)(i_top - 2) * n_cs + foff[q]];
-  __syncthreads();
-  if (cl > 1) cluster_barrier();
-
-  auto step = [&](const int i, double(&fs)[2], double& bz) {
-    // (1) land the far values of step i - 1 (in flight since step i + 2; step i_top has none: the prologue did it),
-    //     then re-issue the set for step i - 3 (rows >= i + 1, complete since the last barrier)
-    if (i < i_top && i >= 1) {
-#pragma unroll
-      for (int q = 0; q < 2; q++)
-        if (foff[q] >= 0) G[((i - 1) & 3) * gs + n_near + tid + q * AR_THREADS] = fs[q];
-    }
-    if (i >= 3) {
-#pragma unroll
-      for (int q = 0; q < 2; q++)
-        if (foff[q] >= 0) fs[q] = __ldcg(buffer + (size_t)(i - 3) * n_cs + foff[q]);
-    }
-    // (2) the dot product of this thread's slice of its row: A from registers, x contiguous in shared memory
-    const double* g = G + (i & 3) * gs + sub;
-    double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
-#pragma unroll
-    for (int m = 0; m < MP; m += 4) {
-      acc0 = fma(a[m], g[L * m], acc0);
-      if (m + 1 < MP) acc1 = fma(a[m + 1], g[L * (m + 1)], acc1);
-      if (m + 2 < MP) acc2 = fma(a[m + 2], g[L * (m + 2)], acc2);
-      if (m + 3 < MP) acc3 = fma(a[m + 3], g[L * (m + 3)], acc3);
-    }
-    double acc = (acc0 + acc1) + (acc2 + acc3);
-#pragma unroll
-    for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    // (3) publish row r of step i: to global memory and into the gather vectors of steps i-1, i-2, i-3 of every CTA
-    if (has_row && sub == 0) {
-      const double v = bz + acc;
-      buffer[(size_t)i * n_cs + row0 + r] = v;
-      double* d1 = G + ((i - 1) & 3) * gs + p1;
-      double* d2 = G + ((i - 2) & 3) * gs + p2;
-      double* d3 = G + ((i - 3) & 3) * gs + p3;
-      if (cl == 1) {
-        if (p1 >= 0) *d1 = v;
-        if (p2 >= 0) *d2 = v;
-        if (p3 >= 0) *d3 = v;
-      } else {
-        for (int c = 0; c < cl; c++) {
-          if (p1 >= 0) st_dsmem_f64(d1, c, v);
-          if (p2 >= 0) st_dsmem_f64(d2, c, v);
-          if (p3 >= 0) st_dsmem_f64(d3, c, v);
-        }
-      }
-    }
-    // (4) re-issue the B z register for step i - 2
-    if (i >= 2 && has_row) bz = __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r);
-    if (cl == 1)
-      __syncthreads();
-    else
-      cluster_barrier();
-  };
-
-  for (int i = i_top; i >= 1; i -= 2) {  // i_top = 2 n_ext - 1 is odd
-    step(i, far_s[1], bz_s[1]);
-    step(i - 1, far_s[0], bz_s[0]);
-  }
-}
 
 // ---------------------------------------------------------------------------------------------------------
-// The chain, v4: the same register-resident layout as v3, with the cluster barrier replaced by data-carrying signals.
+// The chain, v4.  A step is bounded by the round trips on its critical path, not by arithmetic, so everything that is not
+// "the previous row" is taken off that path and the rest is made short:
+//   * A lives in REGISTERS.  L lanes share a row (32 / L rows per warp): lane `sub` holds the entries of samples
+//     sub, sub + L, ...  ->  the cross-lane reduction is log2(L) shuffle stages instead of 5 per row;
+//   * the gather vector of step i is a contiguous shared-memory array G[i & 3][n_sample]: whoever produces a value
+//     writes it straight to where its consumers will read it; the stencil rows further back (offsets >= 4) plus the row's
+//     own B z term are fetched from L2 ahead of their use through a register pipeline, so their latency never shows;
+//   * no barrier: data-carrying signals.
 // Every value travels with its own completion: the owner of (row i, column c) sends it with st.async into the gather
 // vectors of steps i-1, i-2, i-3 of every CTA, each store completing bytes on an mbarrier of the DESTINATION CTA.  A
 // gather vector has two mbarriers: EARLY (stencil offsets 2, 3 and the far samples: everything known one step ahead)
@@ -623,16 +479,11 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
 }
 
 template <int L, int MP>
-static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
+static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
                            int n_cs, int n_sample, int n_near, int cl, cudaStream_t stream) {
-  static int use_v3 = -1;  // MATM_AR_V3=1: the barrier-per-step kernel (kept for comparison)
-  if (use_v3 < 0) {
-    const char* e = getenv("MATM_AR_V3");
-    use_v3 = (e && atoi(e)) ? 1 : 0;
-  }
   const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16;
-  auto kernel = use_v3 ? ar_chain_v3_kernel<L, MP> : ar_chain_v4_kernel<L, MP>;
-  if constexpr (L == 8 && MP >= 32) if (!use_v3) {
+  auto kernel = ar_chain_v4_kernel<L, MP>;
+  if constexpr (L == 8 && MP >= 32) {
     // the long chains (n_cs ~ 100-160): the split between the LATE and EARLY registers as a compile-time constant.
     // n_cs bounds the number of offset-1 samples from above, so registers [0, 4 mc) always hold all of them.
     const int mc = (n_cs + 4 * L - 1) / (4 * L);
@@ -659,20 +510,10 @@ static int launch_chain_v3(matm_handle* h, const double* A, const int* esi, cons
 }
 
 // picks (lanes per row, samples per lane, cluster size) for the register-resident kernel; false if it does not fit
-static bool plan_v3(int n_cs, int n_sample, int* L, int* MP, int* cl) {
+static bool plan_v4(int n_cs, int n_sample, int* L, int* MP, int* cl) {
   static const int Ls[4] = {4, 8, 16, 32};
   static const int MPs[4] = {16, 24, 32, 40};
-  static int min_l = -1;  // MATM_AR_MINL: lower bound on the lanes per row (tuning knob; more lanes = shorter per-thread chain)
-  if (min_l < 0) {
-    const char* e = getenv("MATM_AR_MINL");
-    min_l = e ? atoi(e) : 0;
-  }
   for (int li = 0; li < 4; li++) {
-    if (Ls[li] < min_l && li < 3) {
-      // only skip when a larger L still fits the cluster limit
-      const int rows_next = (AR_THREADS / 32) * (32 / Ls[li + 1]);
-      if ((n_cs + rows_next - 1) / rows_next <= 8 && n_sample <= Ls[li + 1] * 40) continue;
-    }
     if (n_sample > Ls[li] * 40) continue;
     int mp = 0;
     for (int mi = 0; mi < 4; mi++)
@@ -710,13 +551,13 @@ extern "C" int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sampl
   {
     int L, mp, cl3;
     if (n_near >= 0 && n_near <= n_sample && n_ext >= 4 && (n_sample - n_near) <= 2 * AR_THREADS &&
-        plan_v3(n_cs, n_sample, &L, &mp, &cl3)) {
-#define V3_CASE(LV, MV) \
+        plan_v4(n_cs, n_sample, &L, &mp, &cl3)) {
+#define V4_CASE(LV, MV) \
   if (L == LV && mp == MV) \
-    return launch_chain_v3<LV, MV>(h, A_dev, esi_dev, csi_dev, buffer_dev, n_ext, n_cs, n_sample, n_near, cl3, st);
-      V3_CASE(4, 16) V3_CASE(4, 24) V3_CASE(4, 32) V3_CASE(4, 40) V3_CASE(8, 16) V3_CASE(8, 24) V3_CASE(8, 32)
-      V3_CASE(8, 40) V3_CASE(16, 24) V3_CASE(16, 32) V3_CASE(16, 40) V3_CASE(32, 24) V3_CASE(32, 32) V3_CASE(32, 40)
-#undef V3_CASE
+    return launch_chain_v4<LV, MV>(h, A_dev, esi_dev, csi_dev, buffer_dev, n_ext, n_cs, n_sample, n_near, cl3, st);
+      V4_CASE(4, 16) V4_CASE(4, 24) V4_CASE(4, 32) V4_CASE(4, 40) V4_CASE(8, 16) V4_CASE(8, 24) V4_CASE(8, 32)
+      V4_CASE(8, 40) V4_CASE(16, 24) V4_CASE(16, 32) V4_CASE(16, 40) V4_CASE(32, 24) V4_CASE(32, 32) V4_CASE(32, 40)
+#undef V4_CASE
     }
   }
   // fallback (v1): smallest cluster whose per-CTA slice of A fits in shared memory; above 8 CTAs A streams from L2

@@ -139,7 +139,7 @@ __device__ __forceinline__ float emission_blend_f32(const SynthParams& P, int ba
 // ---------------------------------------------------------------------------------------------------------
 #define LD_THREADS 256
 #ifndef LD_KA
-#define LD_KA 128  // knots per CTA: 1 (M = 4), 2 (M = 2) or 4 (M = 1) passes of F32_G knots per thread
+#define LD_KA 256  // knots per CTA (the per-knot cell table of all layers is staged once per CTA; 64: 8.9, 128: 8.1, 256: 7.7 ms)
 #endif
 #ifndef LD_MINB
 // CTAs per SM the register allocation is held to.  Measured at C4 (ms per launch): G x LB x MINB = 2x2x4 8.1, 4x1x3 8.6,

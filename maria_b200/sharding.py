@@ -40,6 +40,8 @@ def assert_same_setup(dist, fingerprint):
     import torch
 
     t = torch.as_tensor(np.asarray(fingerprint, dtype=np.float64))
+    if dist.get_backend() == "nccl":
+        t = t.cuda()
     lo, hi = t.clone(), t.clone()
     dist.all_reduce(lo, op=dist.ReduceOp.MIN)
     dist.all_reduce(hi, op=dist.ReduceOp.MAX)

@@ -105,6 +105,23 @@ class Simulation(AtmosphereMixin):
                 obs.atmosphere.initialize(obs)
                 logger.debug(f"Initialized atmosphere in {ttime.monotonic() - t0:.2f} s")
             self.obs_list.append(obs)
+        if det_range is not None:
+            self._check_ranks_agree()
+
+    def _check_ranks_agree(self):
+        """Detector shards of several ranks tile one TOD only if every rank built the same layer geometry (same host RNG
+        stream): under torch.distributed the set-up fingerprints are compared (sharding.assert_same_setup)."""
+        try:
+            import torch.distributed as dist
+        except Exception:
+            return
+        if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+            return
+        from . import sharding
+
+        for obs in self.obs_list:
+            if obs.atmosphere is not None:
+                sharding.assert_same_setup(dist, sharding.setup_fingerprint(obs.atmosphere))
 
     def run(self, units="K_RJ"):
         """:201-211 -- one TOD per plan, in ``units``."""

@@ -231,6 +231,36 @@ def test_c5_six_hour_scan_runs_and_matches_oracle_subset(cuda):
     _check32(tod[sel].cpu().numpy(), ref, sim)
 
 
+def test_c5_six_hour_recurrence_and_fp64_synthesis_match_oracle(cuda):
+    """C5 in validation mode: (1) the AR recurrence of the longest six-hour layer (n_ext > 100 000: > 200 000 dependent
+    float64 steps, six times C4's) against the oracle's chain with identical host noise, 1e-10; (2) the float64 device
+    synthesis on the 1.08 M-sample axis against the oracle fed with the device's layers, 1e-10."""
+    cfg = configs.c5_long(n_det=64, duration=21600.0, sample_rate=50.0)
+    n = cfg["instrument"].dets.n
+    sim = _device(cfg, np.float64, 37, noise="host", geometry="fast")
+    obs, atm = sim.obs_list[0], sim.obs_list[0].atmosphere
+    k = max(atm.processes, key=lambda q: atm.processes[q].n_extrusion * atm.processes[q].n_cross_section)
+    p = atm.processes[k]
+    assert p.n_extrusion > 100000 and p.n_cross_section > 100
+    rng = np.random.default_rng(9)
+    buffer0 = np.zeros((3 * p.n_extrusion, p.n_cross_section))
+    buffer0[2 * p.n_extrusion:] = rng.standard_normal((p.n_extrusion, p.n_cross_section))  # only these rows are read
+    z = rng.standard_normal((2 * p.n_extrusion, p.n_cross_section))
+    dev = p.run(rng=O.ReplayRNG([buffer0, z])).cpu().numpy()
+    q = O.AutoregressiveProcess(p.cross_section, p.extrusion, {}, jitter=1e-8)
+    q.A, q.B = p.A, p.B
+    ref = q.run(O.ReplayRNG([buffer0] + [z[i] for i in range(len(z))]))
+    assert relmax(dev, ref) < TOL64
+    # (2) all processes regenerated (host noise), float64 synthesis of a few detectors over the six hours
+    atm.simulate_pwv()
+    atm.set_gain(np.ones(n))
+    tod = sim._compute_atmospheric_loading(obs, units="K_RJ", apply_gain=True)
+    assert atm.check_flags() == 0 and tod.shape == (n, 1080000)
+    sel = np.array([0, n // 2, n - 1])
+    ref = _oracle_with_layers(cfg, atm, sel, {kk: pp.values for kk, pp in atm.processes.items()})
+    assert relmax(tod[sel].cpu().numpy(), ref) < TOL64
+
+
 def _log_binned_psd(x, rate, n_bins=12):
     """Hann-windowed, linearly detrended periodogram, log-binned (the recipe of maria/plotting/tod.py:100-112)."""
     n = x.shape[-1]

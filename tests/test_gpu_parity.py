@@ -157,3 +157,33 @@ def test_out_of_grid_raises_like_the_reference(cuda):
     atm.generate()
     with pytest.raises(RuntimeError, match="introduced nans"):
         atm.zenith_scaled_pwv
+
+
+def test_3d_model_matches_oracle(cuda):
+    """The coupled "3d" model (extrusion.py:69-77, atmosphere.py:249): ONE autoregressive process over all layers, Matern
+    nu = 1/3, one layer per resolution element of height (20 layers here).  Its process (n_cs = 300, n_sample ~ 590) does
+    not fit the register-resident chain kernel, so this test also covers the general chain kernel (ar_chain_kernel: A
+    slices in shared memory staged by the TMA, cluster barrier per step), the column-sliced beam smoothing of a shared
+    process, and a sampler with more than 16 layers."""
+    case = small_case(n_det=16, duration=8.0, sample_rate=20.0, seed=4, fov_deg=0.2, primary=6.0)
+    kw = dict(max_height=300.0)
+    np.random.seed(case["seed"])
+    res = O.simulate(case["instrument"], case["plan"], case["site"], case["weather"], case["spectrum"], np.random, model="3d",
+                     dtype=np.float64, atmosphere_kwargs=kw)
+    out = {}
+    for dtype in (np.float64, np.float32):
+        np.random.seed(case["seed"])
+        sim = M.Simulation(case["instrument"], case["plan"], case["site"], atmosphere="3d", dtype=dtype,
+                           atmosphere_kwargs=dict(weather=case["weather"], spectrum=case["spectrum"], geometry="exact", **kw))
+        atm = sim.obs_list[0].atmosphere
+        assert len(atm.processes) == 1 and len(atm.layers["h"]) > 16
+        p = atm.processes[0]
+        assert p.n_sample > 512 and p.n_cross_section > 256  # beyond the register-resident kernel
+        tod = sim.run(units="K_RJ")[0]
+        if dtype is np.float64:
+            assert relmax(p.values, res["atmosphere"].processes[0].values) < TOL64
+            assert relmax(atm.zenith_scaled_pwv, res["atmosphere"].zenith_scaled_pwv) < TOL64
+            assert relmax(tod.data["atmosphere"], res["tod_K_RJ"]) < TOL64
+        else:
+            obs = sim.obs_list[0]
+            check32(tod.data["atmosphere"], res["tod_K_RJ"], obs.boresight.t, atm.boresight.t[-1])
