@@ -66,7 +66,13 @@ class DeviceContext:
         self.lib.matm_last_error(self.h, buf, 1024)
         msg = buf.value.decode(errors="replace")
         if rc == _lib.ERR_ARG:
-            raise RuntimeError(msg)
+            # call-order errors are the reference's RuntimeError ("Atmosphere must be initialized ...", atmosphere.py:294-295),
+            # anything else about the arguments is a ValueError (atmosphere.py:48-51, process.py:169-172)
+            if "initialized" in msg or " first" in msg or "not all set" in msg:
+                raise RuntimeError(msg)
+            raise ValueError(msg)
+        if rc == _lib.ERR_TABLE_RANGE:
+            raise ValueError(f"(T0, pwv, el) left the spectrum table: {msg}")
         raise RuntimeError(f"libmaria_atm status {rc}: {msg}")
 
     def stream_ptr(self):

@@ -40,6 +40,9 @@ class Observation:
     """The fields of maria/sim/observation.py:27-102 that the atmosphere path reads."""
 
     def __init__(self, instrument, plan, site, atmosphere=None, atmosphere_kwargs=None):
+        from . import adapters
+
+        instrument, plan, site = adapters.coerce(instrument, plan, site)  # the reference's own objects are accepted
         self.instrument, self.plan, self.site = instrument, plan, site
         self.boresight = Boresight(plan.time, plan.phi, plan.theta)  # :46-52
         dets = instrument.dets
@@ -55,6 +58,10 @@ class Observation:
             kw.setdefault("region", site.region)
             kw.setdefault("altitude", site.altitude)
             kw.setdefault("timestamp", float(np.mean(plan.time)))
+            if "weather" in kw and not isinstance(kw["weather"], (dict, type(None))) and not hasattr(kw["weather"], "data"):
+                kw["weather"] = adapters.weather_from_maria(kw["weather"])  # a maria.weather.Weather
+            if kw.get("spectrum") is not None:
+                kw["spectrum"] = adapters.spectrum_from_maria(kw["spectrum"])
             self.atmosphere = Atmosphere(model=atmosphere, **kw)
 
 
@@ -91,7 +98,7 @@ class Simulation(AtmosphereMixin):
     def __init__(self, instrument, plans, site, atmosphere=None, atmosphere_kwargs=None, dtype=np.float32, noise=False,
                  progress_bars=False, det_range=None, **kwargs):
         self.instrument, self.site = instrument, site
-        self.plans = plans if isinstance(plans, (list, tuple)) else [plans]
+        self.plans = list(plans) if isinstance(plans, (list, tuple)) or type(plans).__name__ == "PlanList" else [plans]
         self.dtype = np.dtype(dtype)
         self.det_range = det_range
         self.disable_progress_bars = not progress_bars

@@ -187,3 +187,25 @@ def test_3d_model_matches_oracle(cuda):
         else:
             obs = sim.obs_list[0]
             check32(tod.data["atmosphere"], res["tod_K_RJ"], obs.boresight.t, atm.boresight.t[-1])
+
+
+def test_unit_carrying_objects_give_the_same_tod(cuda):
+    """``Simulation`` fed with maria-style objects (quantities with units, Band objects with ``nu.Hz``; the real ones are
+    checked on CPU by tests/test_cpu_adapter.py) produces the same bits as with the plain-array views."""
+    from test_cpu_adapter import Q, _Obj
+
+    case = small_case(n_det=32, duration=10.0, sample_rate=50.0, seed=9)
+    d = case["instrument"].dets
+    bands = [_Obj(name=b.name, nu=Q(b.nu / 1e9, "GHz"), tau=b.tau, efficiency=b.efficiency, gain_error=b.gain_error,
+                  center=Q(b.center, "Hz")) for b in d.bands]
+    dets = _Obj(xi=Q(np.degrees(d.xi), "deg"), eta=Q(np.degrees(d.eta), "deg"), band_name=d.band_name, bands=bands, gamma=d.gamma,
+                primary_size=Q(d.primary_size, "m"), band_center=d.band_center)
+    plan = _Obj(time=case["plan"].time, phi=Q(case["plan"].phi, "rad"), theta=Q(case["plan"].theta, "rad"), frame="az/el", roll=0.0)
+    site = _Obj(region=case["site"].region, altitude=Q(case["site"].altitude / 1e3, "km"))
+    out = []
+    for inst, pl, st in [(case["instrument"], case["plan"], case["site"]), (_Obj(dets=dets, name="q"), plan, site)]:
+        np.random.seed(case["seed"])
+        sim = M.Simulation(inst, pl, st, atmosphere="2d", dtype=np.float32,
+                           atmosphere_kwargs=dict(weather=case["weather"], spectrum=case["spectrum"], geometry="exact"))
+        out.append(sim.run(units="K_RJ")[0].data["atmosphere"])
+    assert relmax(out[1], out[0]) < 1e-6  # degrees -> radians round trip moves offsets by an ulp
