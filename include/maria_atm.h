@@ -106,6 +106,10 @@ int matm_set_layer_data(matm_handle* h, int n_layers, const void* const* data_de
 int matm_set_detectors(matm_handle* h, int64_t n_det, const double* offsets_atm_host, const double* offsets_full_host,
                        const int32_t* band_index_host, const double* mueller00_host, const double* gain_host);
 
+/* Replaces the per-detector gain factors only (simulation.py:239-241 draws new ones for every observation): one
+ * host -> device copy ordered on `stream`; does not synchronise the device. */
+int matm_set_gain(matm_handle* h, const double* gain_host, void* stream);
+
 /* Spectrum tables (band.py:235-255,264-300; spectrum/atmosphere.py:97-104).  emission/opacity: (nT, npwv, nel, nnu)
  * float64 row-major; passband: (n_bands, nnu) = Band.passband(side_nu); T0 = weather.temperature[0];
  * cal_T0 / cal_pwv = the rounded metadata values TOD.to uses (tod.py:90-104); cal_factor[b] = 0.5 if the band is
@@ -130,7 +134,7 @@ int matm_synthesize(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, 
 
 /* Tuning of the float path of matm_synthesize: it runs per chunk of detector tiles as two kernels (loading at the
  * atmosphere-rate knots into a scratch of `chunk_mib` MiB, then spline + evaluation + calibration at the full rate);
- * overlap != 0 alternates consecutive chunks between two scratch buffers and two internal streams.  Defaults: 32, 1. */
+ * overlap != 0 alternates consecutive chunks between two scratch buffers and two internal streams.  Defaults: 1024, 1. */
 int matm_set_tuning(matm_handle* h, int chunk_mib, int overlap);
 
 /* Per-kernel timing of the float path (measurement only): with enable != 0 every chunk's two launches are bracketed by

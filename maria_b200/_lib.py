@@ -40,6 +40,7 @@ SIGNATURES = {
     "matm_set_layers": (C.c_int, [vp, C.c_int, C.POINTER(LayerDesc), C.c_double]),
     "matm_set_layer_data": (C.c_int, [vp, C.c_int, C.POINTER(vp)]),
     "matm_set_detectors": (C.c_int, [vp, C.c_int64, c_dp, c_dp, c_ip, c_dp, c_dp]),
+    "matm_set_gain": (C.c_int, [vp, c_dp, vp]),
     "matm_set_bands": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
                                  c_dp, C.c_double, C.c_double, C.c_double, c_dp]),
     "matm_zenith_pwv": (C.c_int, [vp, C.c_int64, C.c_int64, vp, vp]),

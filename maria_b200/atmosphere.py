@@ -230,13 +230,22 @@ class Atmosphere:
                  "philox": counter-based RNG on the device, keyed by ``seed``
       rng        object with ``standard_normal(size)``; default the global ``np.random`` like the reference
       geometry   "exact" | "fast" | "auto": footprint alignment on all points (reference) or on their 3-D hull
+      obs_index  index of the observation (plan) this atmosphere belongs to: part of the Philox subsequence, so that the
+                 plans of one Simulation draw independent atmospheres from one seed
+      layer_exchange  under torch.distributed: rank r generates only the processes k with k % world == r (AR chain + beam
+                 smoothing) and the smoothed layers are broadcast (NCCL over NVLink; SURVEY.md section 8e option B)
+                 instead of every rank regenerating every layer.  Philox noise only (host noise has a global draw order).
+
+    Philox noise is keyed by (seed, obs_index, realisation, process): every ``simulate_pwv()`` / ``generate_async()`` is a
+    fresh realisation (``realisation`` counts them, like successive draws from the reference's global ``np.random``);
+    assign ``atm.realisation = n`` to reproduce realisation n.
     """
 
     def __init__(self, model="2d", timestamp=None, region="princeton", altitude=None, weather=None,
                  weather_quantiles=None, weather_source="era5", spectrum_source="am", pwv_rms_frac=0.03,
                  max_height=5e3, timestep=None, interpolation_method="linear", disable_progress_bars=False, *,
                  spectrum=None, device=0, precision="fp32", noise="host", seed=1234, rng=None, geometry="auto",
-                 pipeline_depth=1):
+                 pipeline_depth=1, obs_index=0, layer_exchange=False):
         if model not in SUPPORTED_MODELS_LIST:
             raise ValueError(f"Invalid model '{model}'. Supported models are {SUPPORTED_MODELS_LIST}.")
         if noise not in ("host", "philox"):
@@ -260,6 +269,10 @@ class Atmosphere:
         self.rng = rng if rng is not None else np.random
         self.geometry = geometry
         self.pipeline_depth = max(1, int(pipeline_depth))  # realisations whose AR chains may be in flight at once
+        self.obs_index, self.realisation = int(obs_index), 0
+        self.layer_exchange = bool(layer_exchange)
+        if self.layer_exchange and noise != "philox":
+            raise ValueError("layer_exchange needs noise='philox' (host noise is drawn in one global order)")
         self._initialized = False
         self._generated = False
         self._layers_set_once = False
@@ -386,10 +399,11 @@ class Atmosphere:
     def set_gain(self, gain):
         """Per-detector gain factors exp(gain_error N(0,1)) (simulation.py:239-241)."""
         ctx, dets = self.ctx, self._obs.instrument.dets
-        band_index, off_atm, off_full, mu = self._det_host
         g = _lib.f64(gain)
-        ctx.check(ctx.lib.matm_set_detectors(ctx.h, dets.n, _lib.dptr(off_atm), _lib.dptr(off_full), _lib.iptr(band_index),
-                                             _lib.dptr(mu), _lib.dptr(g)))
+        if g.shape != (dets.n,):
+            raise ValueError(f"gain must have one entry per detector ({dets.n}), got {g.shape}")
+        self._gain_host = g  # keep the buffer alive until the copy has been issued
+        ctx.check(ctx.lib.matm_set_gain(ctx.h, _lib.dptr(g), ctx.stream_ptr()))
 
     # ---------------------------------------------------------------------------------------------------------
     def generate(self):
@@ -420,15 +434,30 @@ class Atmosphere:
             self._build_layer_plan()
         slot = self._issued % self.pipeline_depth
         self._issued += 1
+        realisation = self.realisation
+        self.realisation += 1
+        rank, world = self._rank_world()
         for k, process in self.processes.items():
+            if self.layer_exchange and k % world != rank:
+                continue  # another rank generates this process; its layers arrive in finish_generate
             stream = self._streams[(slot, k)]
             stream.wait_event(fork)
             with tc.cuda.stream(stream):
                 if self.noise == "host":
                     process.run(rng=self.rng, slot=slot)
                 else:
-                    process.run(seed=self.seed, subsequence=k, slot=slot)
+                    # subsequence = (observation, realisation, process): no two draws of a Simulation share a Philox stream
+                    process.run(seed=self.seed, subsequence=(self.obs_index << 44) | (realisation << 12) | k, slot=slot)
         self._pending_slots.append(slot)
+
+    def _rank_world(self):
+        if not self.layer_exchange:
+            return 0, 1
+        import torch.distributed as dist
+
+        if not (dist.is_available() and dist.is_initialized()):
+            return 0, 1
+        return dist.get_rank(), dist.get_world_size()
 
     @property
     def _pending(self):
@@ -447,6 +476,7 @@ class Atmosphere:
         target = 1 - self._layer_cur if self._layers_set_once else self._layer_cur
         readers_done = self._reader_done[target]
         slot = self._pending_slots.pop(0)
+        rank, world = self._rank_world()
         for k, process in self.processes.items():
             stream = self._streams[(slot, k)]
             if readers_done is not None:
@@ -457,9 +487,17 @@ class Atmosphere:
                 st = ctx.stream_ptr()
                 for (li, col0, n_cols, sig_e, sig_x) in self._layer_plan[k]:
                     out, scratch = self._layer_sets[target][li]
-                    ctx.check(ctx.lib.matm_smooth_layer(ctx.h, process.values_device.data_ptr(), process.n_extrusion,
-                                                        process.n_cross_section, col0, n_cols, sig_e, sig_x,
-                                                        out.data_ptr(), scratch.data_ptr(), st))
+                    if k % world == rank:
+                        ctx.check(ctx.lib.matm_smooth_layer(ctx.h, process.values_device.data_ptr(), process.n_extrusion,
+                                                            process.n_cross_section, col0, n_cols, sig_e, sig_x,
+                                                            out.data_ptr(), scratch.data_ptr(), st))
+                    if world > 1:
+                        # the one exchange step of the path: the owner's smoothed layer to every rank, on the process's
+                        # own stream, i.e. underneath the synthesis that still reads the other set of layer buffers
+                        import torch.distributed as dist
+
+                        dist.broadcast(out, src=k % world)
+                        self.exchanged_bytes = getattr(self, "exchanged_bytes", 0) + out.numel() * out.element_size()
             cur.wait_stream(stream)
         self._layer_cur = target
         if not getattr(self, "_layers_set", False):

@@ -97,7 +97,8 @@ struct matm_handle {
   bool timing = false;
   std::vector<cudaEvent_t> tev;  // triples (before loading, between, after evaluation) per chunk
   size_t tev_used = 0;
-  int chunk_mib = 32;   // scratch per chunk; two chunks in flight must fit the 126 MB L2 next to the layers
+  int chunk_mib = 1024; // scratch per chunk.  Measured at C4 (ms per step): 16 MiB 28.6, 32 28.55, 128 28.2, 1024 28.0, one
+                        // piece 28.0: keeping the scratch L2-resident buys nothing, fewer launch tails do
   bool overlap = true;  // alternate chunks between two side streams
   cudaStream_t yk_stream[2] = {nullptr, nullptr};
   cudaEvent_t yk_ev[4] = {nullptr, nullptr, nullptr, nullptr};

@@ -398,6 +398,17 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   return MATM_OK;
 }
 
+extern "C" int matm_set_gain(matm_handle* h, const double* gain_host, void* stream) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (!h->have_dets) MATM_FAIL_ARG(h, "matm_set_gain: call matm_set_detectors first");
+  if (!gain_host) MATM_FAIL_ARG(h, "matm_set_gain: null pointer");
+  // one copy into the existing buffer, ordered on the caller's stream: no reallocation, no device-wide synchronisation,
+  // the processing order of the detectors stays cached
+  MATM_CUDA(h, cudaMemcpyAsync(h->gain, gain_host, (size_t)h->P.n_det * sizeof(double), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  return MATM_OK;
+}
+
 static inline uint32_t spread_bits16(uint32_t v) {  // 16 bits -> every other bit of 32
   v = (v | (v << 8)) & 0x00FF00FFu;
   v = (v | (v << 4)) & 0x0F0F0F0Fu;

@@ -105,8 +105,10 @@ class Simulation(AtmosphereMixin):
         akw = dict(atmosphere_kwargs or {})
         akw.setdefault("precision", "fp64" if self.dtype == np.float64 else "fp32")
         self.obs_list = []
-        for plan in self.plans:  # :142-157
-            obs = Observation(instrument, plan, site, atmosphere=atmosphere, atmosphere_kwargs=akw)
+        for obs_index, plan in enumerate(self.plans):  # :142-157
+            akw_i = dict(akw)
+            akw_i.setdefault("obs_index", obs_index)  # plans draw independent atmospheres from one Philox seed
+            obs = Observation(instrument, plan, site, atmosphere=atmosphere, atmosphere_kwargs=akw_i)
             if obs.atmosphere is not None:
                 t0 = ttime.monotonic()
                 obs.atmosphere.initialize(obs)
@@ -145,12 +147,12 @@ class Simulation(AtmosphereMixin):
             raise RuntimeError("this build synthesises the atmosphere field only: pass atmosphere='2d'")
         dets = obs.instrument.dets
         self._simulate_atmosphere(obs)  # :216-221 (generates the layers)
+        gain_error = np.exp(dets.gain_error * atm.rng.standard_normal(size=dets.n))  # :239-241
+        atm.set_gain(gain_error)  # one asynchronous copy (matm_set_gain): nothing below waits for the device
         if prefetch is not None and prefetch.noise == "philox" and prefetch is not atm:
             # device noise has no host draw order to respect: start the next observation's AR chains now, so that they
             # run (on a handful of SMs) underneath this observation's synthesis kernel
             prefetch.generate_async()
-        gain_error = np.exp(dets.gain_error * atm.rng.standard_normal(size=dets.n))  # :239-241
-        atm.set_gain(gain_error)
         det0, n_det = self.det_range if self.det_range is not None else (0, dets.n)
         data = self._compute_atmospheric_loading(obs, det0, n_det, units=units, apply_gain=True)
         obs.loading["atmosphere"] = data

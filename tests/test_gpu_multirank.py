@@ -29,14 +29,14 @@ def _case():
     return configs.c4_atlast(n_det=1000, duration=240.0, sample_rate=50.0)
 
 
-def _simulate(det_range, device, seed_offset=0, units="K_RJ"):
+def _simulate(det_range, device, seed_offset=0, exchange=False):
     import maria_b200 as M
 
     cfg = _case()
     np.random.seed(41 + seed_offset)
     sim = M.Simulation(cfg["instrument"], cfg["plan"], cfg["site"], atmosphere="2d", dtype=np.float32, det_range=det_range,
                        atmosphere_kwargs=dict(weather=cfg["weather"], spectrum=cfg["spectrum"], noise="philox", seed=7,
-                                              geometry="fast", device=device))
+                                              geometry="fast", device=device, layer_exchange=exchange))
     return sim
 
 
@@ -58,6 +58,11 @@ def _worker(rank, world, port, out_dir):
     shard = tod.data["atmosphere"]
     assert shard.shape[0] == cnt
     np.save(os.path.join(out_dir, f"shard{rank}.npy"), shard)
+    # SURVEY 8e option B: rank r generates the processes k % 2 == r only, the smoothed layers are broadcast
+    sim_x = _simulate((det0, cnt), device, exchange=True)
+    atm_x = sim_x.obs_list[0].atmosphere
+    np.save(os.path.join(out_dir, f"xshard{rank}.npy"), sim_x.run(units="K_RJ")[0].data["atmosphere"])
+    open(os.path.join(out_dir, f"xbytes{rank}"), "w").write(str(getattr(atm_x, "exchanged_bytes", 0)))
     # a rank with a different host seed builds a different geometry: Simulation must refuse
     caught = False
     try:
@@ -83,3 +88,8 @@ def test_two_processes_tile_the_single_process_tod_bit_for_bit(cuda, tmp_path):
     assert np.array_equal(np.concatenate(parts, axis=0), full)
     assert np.isfinite(full).all() and full.std() > 0
     assert all(open(tmp_path / f"caught{r}").read() == "True" for r in range(world))
+    # exchanged layers are bit-identical to self-generated ones, hence so are the shards
+    xparts = [np.load(tmp_path / f"xshard{r}.npy") for r in range(world)]
+    assert np.array_equal(np.concatenate(xparts, axis=0), full)
+    layer_bytes = sum(4 * p.n_extrusion * p.n_cross_section for p in sim.obs_list[0].atmosphere.processes.values())
+    assert all(int(open(tmp_path / f"xbytes{r}").read()) == layer_bytes for r in range(world))

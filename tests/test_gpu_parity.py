@@ -136,14 +136,29 @@ def test_philox_layers_have_matern_structure_function(cuda):
         sf.append([np.mean((v[l:] - v[:-l]) ** 2) for l in lags])
     expected_sf = 2 * (1 - p.callback(lags * p.extrusion_res))
     assert np.all(np.abs(np.mean(sf, axis=0) / expected_sf - 1) < 0.2), (np.mean(sf, axis=0), expected_sf)
-    atm.seed = 5  # the same seed reproduces the same layers, a different one does not
+    # (seed, realisation) reproduces the layers; the next realisation of the same seed and another seed do not: successive
+    # simulate_pwv() calls are fresh draws, like the reference's global np.random stream
+    atm.seed, atm.realisation = 5, 0
     atm.generate()
     a = p.values.copy()
     atm.generate()
+    assert atm.realisation == 2 and not np.array_equal(a, p.values)
+    atm.realisation = 0
+    atm.generate()
     assert np.array_equal(a, p.values)
-    atm.seed = 6
+    atm.seed, atm.realisation = 6, 0
     atm.generate()
     assert not np.array_equal(a, p.values)
+
+
+def test_plans_of_one_simulation_draw_independent_atmospheres(cuda):
+    """Two identical plans in one Simulation with one Philox seed: different observations, different atmospheres."""
+    case = small_case(n_det=16, duration=10.0, sample_rate=50.0, seed=3)
+    np.random.seed(3)
+    sim = M.Simulation(case["instrument"], [case["plan"], case["plan"]], case["site"], atmosphere="2d",
+                       atmosphere_kwargs=dict(weather=case["weather"], spectrum=case["spectrum"], noise="philox", seed=99))
+    t0, t1 = sim.run(units="K_RJ")
+    assert t0.shape == t1.shape and not np.array_equal(t0.data["atmosphere"], t1.data["atmosphere"])
 
 
 def test_out_of_grid_raises_like_the_reference(cuda):
