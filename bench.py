@@ -508,7 +508,14 @@ def run_b200(args):
         raise RuntimeError("bench.py needs a CUDA device: the CUDA path has no CPU fallback")
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+        # the only data-path collective is a 26 MB layer exchange per realisation: two CTAs per collective are plenty, and
+        # NCCL kernels waiting for a peer must not hold the SMs the synthesis runs on
+        opts = dist.ProcessGroupNCCL.Options()
+        try:
+            opts.config.min_ctas, opts.config.max_ctas = 1, 2
+        except Exception:
+            pass
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"), pg_options=opts)
     from maria_b200 import sharding
 
     cfg = build_config(args, world)

@@ -153,6 +153,25 @@ int matm_synthesize_host(matm_handle* h, int64_t det0, int64_t n_det, void* out_
 int matm_calibrate(matm_handle* h, int64_t det0, int64_t n_det, const void* in_dev, void* out_dev, int to_units,
                    void* stream);
 
+/* ---- consumers of the path's intermediates, tile-wise on the device -------------- */
+/* Map step (sim/map.py:117-133): out_dev (n_det, n_t) in the handle's dtype = 1e12 k_B * compute_transmission_integral
+ * (band.py:235-255) of each detector's band over the channel [nu_min_Hz, nu_max_Hz), looked up at (T0, zenith_scaled_pwv
+ * upsampled linearly to the full rate (sim/atmosphere.py:30-37), full-rate elevation of the detector): pW per K_RJ.  The
+ * (n_det, n_t) float64 zenith_scaled_pwv of the reference is never materialised. */
+int matm_transmission(matm_handle* h, int64_t det0, int64_t n_det, double nu_min_Hz, double nu_max_Hz, void* out_dev,
+                      void* stream);
+
+/* Noise step (sim/noise.py:35-37,52-61): out = 1e12 * (NEP[band] + NEP_per_loading[band] * loading) * unscaled_noise, all
+ * (n_det, n_t) in the handle's dtype, loading in pW, NEP in W sqrt(s); nep_host / nep_per_loading_host: (n_bands,).
+ * In place allowed (out_dev == noise_dev). */
+int matm_noise_scale(matm_handle* h, int64_t det0, int64_t n_det, const void* loading_dev, const void* noise_dev,
+                     const double* nep_host, const double* nep_per_loading_host, void* out_dev, void* stream);
+
+/* obs.coords on demand (sim/observation.py:55-58 -> coords/transforms.py:10-29): float64 az / el (n_det, n_j) of the
+ * detectors [det0, det0 + n_det) at the full-rate samples [j0, j0 + n_j); either output may be NULL. */
+int matm_pointing(matm_handle* h, int64_t det0, int64_t n_det, int64_t j0, int64_t n_j, double* az_dev, double* el_dev,
+                  void* stream);
+
 /* ---- error flags --------------------------------------------------------------------------------------- */
 /* Reads (and clears) the device flag word; synchronises the device.  status = MATM_OK, MATM_ERR_OUT_OF_GRID or
  * MATM_ERR_TABLE_RANGE; layer/det/sample describe the first recorded out-of-grid sample. */

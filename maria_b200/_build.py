@@ -8,7 +8,7 @@ import subprocess
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libmaria_atm.so")
-SOURCES = ["matm_core.cu", "matm_ar.cu", "matm_smooth.cu", "matm_setup.cu", "matm_synth.cu"]
+SOURCES = ["matm_core.cu", "matm_ar.cu", "matm_smooth.cu", "matm_setup.cu", "matm_synth.cu", "matm_consumers.cu"]
 HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join("..", "..", "include", "maria_atm.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--use_fast_math=false",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

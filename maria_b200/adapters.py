@@ -184,8 +184,7 @@ def install():
         atm.simulate_pwv(obs.instrument)
         ctx, n_det, n_t = atm.ctx, atm._obs.instrument.dets.n, len(atm._obs.boresight.t)
 
-        def upsampled(det0=0, n=None):
-            n = n_det - det0 if n is None else n
+        def upsampled(det0, n):
             zp = atm.zenith_pwv_device(det0, n)
             out = ctx.empty((n, n_t), ctx.torch.float64)
             ctx.check(ctx.lib.matm_upsample_linear(ctx.h, zp.data_ptr(), n, out.data_ptr(), ctx.stream_ptr()))

@@ -192,18 +192,29 @@ class LazyCoords:
         self.t, self._az_b, self._el_b, self._offsets = t, az_b, el_b, offsets
         self.shape = (len(offsets), len(t))
 
+    def bind_device(self, atmosphere):
+        """Evaluate on the GPU from now on: ``az`` / ``el`` become sliceable lazy arrays (``coords.el[100:132, ::50]``
+        touches 32 detectors), nothing of size n_det x n_t is held anywhere."""
+        self._atm = atmosphere
+
     def _eval(self):
         if not hasattr(self, "_az"):
             self._az, self._el = host.offsets_to_az_el(self._offsets, self._az_b, self._el_b)
         return self._az, self._el
 
+    def _lazy(self, which):
+        from .sim import LazyArray
+
+        atm = self._atm
+        return LazyArray(self.shape, np.float64, lambda det0, n: atm.pointing(det0, n, az=which == 0, el=which == 1)[which])
+
     @property
     def az(self):
-        return self._eval()[0]
+        return self._lazy(0) if getattr(self, "_atm", None) is not None else self._eval()[0]
 
     @property
     def el(self):
-        return self._eval()[1]
+        return self._lazy(1) if getattr(self, "_atm", None) is not None else self._eval()[1]
 
 
 class Boresight:
@@ -491,14 +502,30 @@ class Atmosphere:
                         ctx.check(ctx.lib.matm_smooth_layer(ctx.h, process.values_device.data_ptr(), process.n_extrusion,
                                                             process.n_cross_section, col0, n_cols, sig_e, sig_x,
                                                             out.data_ptr(), scratch.data_ptr(), st))
-                    if world > 1:
-                        # the one exchange step of the path: the owner's smoothed layer to every rank, on the process's
-                        # own stream, i.e. underneath the synthesis that still reads the other set of layer buffers
-                        import torch.distributed as dist
+            if world == 1:
+                cur.wait_stream(stream)
+        if world > 1:
+            # The one exchange step of the path (SURVEY.md section 8e option B): once this rank's layers are smoothed, every
+            # owner's segment of the flat layer buffer goes to all ranks -- `world` broadcasts on one side stream,
+            # underneath the synthesis that still reads the other set of layer buffers.  (One collective per layer on the
+            # process streams was measured first: the waiting NCCL kernels held SMs and slowed the synthesis by 40 %.)
+            import torch.distributed as dist
 
-                        dist.broadcast(out, src=k % world)
-                        self.exchanged_bytes = getattr(self, "exchanged_bytes", 0) + out.numel() * out.element_size()
-            cur.wait_stream(stream)
+            if not hasattr(self, "_xstream"):
+                self._xstream = tc.cuda.Stream(device=ctx.device, priority=-1)
+            xs = self._xstream
+            if readers_done is not None:
+                xs.wait_event(readers_done)
+            for k in self.processes:
+                if k % world == rank:
+                    xs.wait_stream(self._streams[(slot, k)])
+            flat = self._flat_sets[target]
+            with tc.cuda.stream(xs):
+                for r, (off, n) in enumerate(self._owner_segments):
+                    if n:
+                        dist.broadcast(flat[off:off + n], src=r)
+                        self.exchanged_bytes = getattr(self, "exchanged_bytes", 0) + n * flat.element_size()
+            cur.wait_stream(xs)
         self._layer_cur = target
         if not getattr(self, "_layers_set", False):
             self.set_layers()
@@ -523,7 +550,9 @@ class Atmosphere:
         """Per layer: its columns in the process, the beam-smoothing widths in cells (atmosphere.py:328-339) and the
         device buffers (smoothed layer in the context's dtype + float64 scratch)."""
         ctx, L, dets = self.ctx, self.layers, self._obs.instrument.dets
+        rank, world = self._rank_world()
         self._layer_plan = {}
+        shapes = {}
         for k, process in self.processes.items():
             plan = []
             for li in process.layer_index:
@@ -531,10 +560,26 @@ class Atmosphere:
                 col0, n_cols = int(cols[0]), len(cols)
                 beam_sigma = host.gaussian_beam_physical_fwhm(dets.primary_size, L["z"][li], dets.band_center).mean() / 2.355
                 plan.append((int(li), col0, n_cols, float(beam_sigma / process.extrusion_res), float(beam_sigma / L["res"][li])))
-                for ls in self._layer_sets:
-                    ls[int(li)] = (ctx.empty((process.n_extrusion, n_cols)),
-                                   ctx.empty((process.n_extrusion, n_cols), ctx.torch.float64))
+                shapes[int(li)] = (k, process.n_extrusion, n_cols)
             self._layer_plan[k] = plan
+        # Every set of smoothed layers is ONE flat buffer, the layers of the processes of one owner rank (k % world)
+        # contiguous: under layer_exchange the exchange is then one broadcast per owner (one rank: plain views).
+        order = sorted(shapes, key=lambda li: (shapes[li][0] % world, li))
+        total = sum(shapes[li][1] * shapes[li][2] for li in order)
+        self._flat_sets, self._owner_segments = [], []
+        for ls in self._layer_sets:
+            flat = ctx.empty((total,))
+            self._flat_sets.append(flat)
+            off = 0
+            for li in order:
+                k, n_ext, n_cols = shapes[li]
+                ls[li] = (flat[off:off + n_ext * n_cols].view(n_ext, n_cols), ctx.empty((n_ext, n_cols), ctx.torch.float64))
+                off += n_ext * n_cols
+        off = 0
+        for r in range(world):
+            n = sum(shapes[li][1] * shapes[li][2] for li in order if shapes[li][0] % world == r)
+            self._owner_segments.append((off, n))
+            off += n
 
     def set_layers(self):
         """Hand the layer geometry (height, transform, grids, wind) and the device layers to the sampler."""
@@ -601,6 +646,41 @@ class Atmosphere:
         ctx.check(ctx.lib.matm_synthesize_host(ctx.h, det0, n_det, ptr, _lib.UNITS_KRJ if units == "K_RJ" else _lib.UNITS_PW,
                                                1 if apply_gain else 0))
         return out_host
+
+    # ---- consumers of the path's intermediates, tile-wise on the device ----
+    def transmission(self, nu_min_Hz=0.0, nu_max_Hz=np.inf, det0=0, n_det=None, out=None):
+        """pW per K_RJ of the frequency channel [nu_min, nu_max) for the map step (sim/map.py:117-133): (n_det, n_t) in
+        the context's dtype, on the device; zenith_scaled_pwv is sampled and upsampled inside the kernel."""
+        ctx = self.ctx
+        n_det = self._obs.instrument.dets.n - det0 if n_det is None else n_det
+        if out is None:
+            out = ctx.empty((n_det, len(self._obs.boresight.t)))
+        ctx.check(ctx.lib.matm_transmission(ctx.h, det0, n_det, float(nu_min_Hz), float(min(nu_max_Hz, 1e300)), out.data_ptr(),
+                                            ctx.stream_ptr()))
+        self._mark_readers()
+        return out
+
+    def noise_scale(self, loading, noise, nep, nep_per_loading, det0=0, out=None):
+        """1e12 (NEP + NEP_per_loading loading) noise per band (sim/noise.py:35-37,60); device tensors in the context's
+        dtype, ``nep`` / ``nep_per_loading`` per band in W sqrt(s), in the order of ``dets.bands``."""
+        ctx = self.ctx
+        out = ctx.torch.empty_like(noise) if out is None else out
+        a, b = _lib.f64(nep), _lib.f64(nep_per_loading)
+        ctx.check(ctx.lib.matm_noise_scale(ctx.h, det0, loading.shape[0], loading.data_ptr(), noise.data_ptr(), _lib.dptr(a),
+                                           _lib.dptr(b), out.data_ptr(), ctx.stream_ptr()))
+        return out
+
+    def pointing(self, det0=0, n_det=None, j0=0, n_j=None, az=True, el=True):
+        """Full-rate az / el of a detector range over a sample range (obs.coords, observation.py:55-58), float64, on the
+        device, evaluated on demand."""
+        ctx = self.ctx
+        n_det = self._obs.instrument.dets.n - det0 if n_det is None else n_det
+        n_j = len(self._obs.boresight.t) - j0 if n_j is None else n_j
+        a = ctx.empty((n_det, n_j), ctx.torch.float64) if az else None
+        e = ctx.empty((n_det, n_j), ctx.torch.float64) if el else None
+        ctx.check(ctx.lib.matm_pointing(ctx.h, det0, n_det, j0, n_j, a.data_ptr() if az else None, e.data_ptr() if el else None,
+                                        ctx.stream_ptr()))
+        return a, e
 
     def simulate_pwv(self, instrument=None):
         """atmosphere.py:293-380.  Generates the layers; ``zenith_scaled_pwv`` is evaluated when read."""

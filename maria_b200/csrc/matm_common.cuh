@@ -107,6 +107,12 @@ struct matm_handle {
   double *det_atm = nullptr, *det_full = nullptr, *mueller00 = nullptr, *gain = nullptr;
   int32_t* band_index = nullptr;
   double *side_pwv = nullptr, *side_el = nullptr, *G2 = nullptr, *H1 = nullptr;
+  // kept for the consumers of the path (matm_consumers.cu)
+  double *opacity = nullptr, *passband = nullptr, *side_nu = nullptr, *az_full = nullptr, *det_v = nullptr, *H3 = nullptr;
+  std::vector<double> nu_host;
+  int nT = 0, nnu = 0, iT = 0;
+  double wT = 0.0;
+  bool T_ok = false;
   void* tabR = nullptr;  // one allocation holding the R-typed tables
   // processing order of the detectors of a requested range (spatially coherent tiles; matm_detector_order)
   std::vector<double> det_xy_host;  // (n_det, 2) the atmosphere's offsets, kept for the ordering

@@ -64,6 +64,12 @@ extern "C" int matm_destroy(matm_handle* h) {
   cudaFree(h->G2);
   cudaFree(h->H1);
   cudaFree(h->tabR);
+  cudaFree(h->opacity);
+  cudaFree(h->passband);
+  cudaFree(h->side_nu);
+  cudaFree(h->az_full);
+  cudaFree(h->det_v);
+  cudaFree(h->H3);
   for (auto& kv : h->det_order) {
     cudaFree(kv.second.order);
     cudaFree(kv.second.tile_m);

@@ -141,13 +141,20 @@ extern "C" int matm_set_scan(matm_handle* h, int n_t_atm, const double* t_atm_ho
   for (int64_t j = 0; j < n_t; j++)
     if (!isfinite(el_host[j]) || !isfinite(t_host[j])) MATM_FAIL_ARG(h, "matm_set_scan: full-rate time / elevation must be finite");
   if (n_t > (int64_t)INT32_MAX) MATM_FAIL_ARG(h, "matm_set_scan: more than 2^31 - 1 samples per detector; split the scan in time");
-  (void)az_host;  // the full-rate azimuth does not enter the path (only the elevation does, tod.py:126-133)
+  // the full-rate azimuth does not enter the synthesis (only the elevation does, tod.py:126-133); it is kept for
+  // matm_pointing (obs.coords on demand)
   const double t_atm0 = t_atm_host[0];
   double *az_d = nullptr, *el_d = nullptr;
   int rc;
   if ((rc = matm_upload(h, &az_d, az_atm_host, (size_t)n_t_atm))) return rc;
   if ((rc = matm_upload(h, &el_d, el_atm_host, (size_t)n_t_atm))) return rc;
   if ((rc = matm_upload(h, &h->el_full, el_host, (size_t)n_t))) return rc;
+  if (az_host) {
+    if ((rc = matm_upload(h, &h->az_full, az_host, (size_t)n_t))) return rc;
+  } else if (h->az_full) {
+    cudaFree(h->az_full);
+    h->az_full = nullptr;
+  }
   if ((rc = matm_upload(h, &h->el_rng, (const double*)nullptr, (size_t)n_t_atm * 2))) return rc;
   if ((rc = matm_upload(h, &h->knot_f, (const float4*)nullptr, (size_t)n_t_atm))) return rc;
   if ((rc = matm_upload(h, &h->samp_w, (const float4*)nullptr, (size_t)n_t))) return rc;
@@ -305,7 +312,8 @@ extern "C" int matm_set_layers(matm_handle* h, int n_layers, const matm_layer_de
 
 // ---- detectors -------------------------------------------------------------------------------------------
 __global__ void det_kernel(const double* __restrict__ off_atm, const double* __restrict__ off_full, int64_t n,
-                           double* __restrict__ det_atm, double* __restrict__ det_full, double* __restrict__ det_cal) {
+                           double* __restrict__ det_atm, double* __restrict__ det_full, double* __restrict__ det_cal,
+                           double* __restrict__ det_v) {
   int64_t d = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= n) return;
   {
@@ -333,6 +341,7 @@ __global__ void det_kernel(const double* __restrict__ off_atm, const double* __r
     const double rho = sqrt(u * u + w * w), q = sr * sp;
     det_cal[2 * d + 0] = atan2(u, w);
     det_cal[2 * d + 1] = q * q / (1.0 + rho);
+    det_v[d] = q;  // sin r sin p: the azimuth of the line of sight is atan2(v, Re q) + az_b (transforms.py:10-29)
   }
 }
 
@@ -362,6 +371,7 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
   if ((rc = matm_upload(h, &h->det_atm, (const double*)nullptr, (size_t)n_det * 4))) return rc;
   if ((rc = matm_upload(h, &h->det_full, (const double*)nullptr, (size_t)n_det * 2))) return rc;
   if ((rc = matm_upload(h, &h->det_cal, (const double*)nullptr, (size_t)n_det * 2))) return rc;
+  if ((rc = matm_upload(h, &h->det_v, (const double*)nullptr, (size_t)n_det))) return rc;
   if ((rc = matm_upload(h, &h->band_index, band_index_host, (size_t)n_det))) return rc;
   if ((rc = matm_upload(h, &h->mueller00, mueller00_host, (size_t)n_det))) return rc;
   std::vector<double> ones;
@@ -370,7 +380,7 @@ extern "C" int matm_set_detectors(matm_handle* h, int64_t n_det, const double* o
     gain_host = ones.data();
   }
   if ((rc = matm_upload(h, &h->gain, gain_host, (size_t)n_det))) return rc;
-  det_kernel<<<(unsigned)((n_det + 255) / 256), 256>>>(oa, of, n_det, h->det_atm, h->det_full, h->det_cal);
+  det_kernel<<<(unsigned)((n_det + 255) / 256), 256>>>(oa, of, n_det, h->det_atm, h->det_full, h->det_cal, h->det_v);
   MATM_LAUNCHED(h);
   MATM_CUDA(h, cudaDeviceSynchronize());
   cudaFree(oa);
@@ -617,9 +627,20 @@ extern "C" int matm_set_bands(matm_handle* h, int n_bands, int nT, int npwv, int
   MATM_LAUNCHED(h);
   MATM_CUDA(h, cudaDeviceSynchronize());
   cudaFree(em);
-  cudaFree(op);
-  cudaFree(pb);
-  cudaFree(nu);
+  // the opacity table, the passbands and the frequency axis stay on the device: the map-step transmission of a frequency
+  // channel (matm_transmission; sim/map.py:117-133) folds them again over [nu_min, nu_max)
+  cudaFree(h->opacity);
+  cudaFree(h->passband);
+  cudaFree(h->side_nu);
+  h->opacity = op;
+  h->passband = pb;
+  h->side_nu = nu;
+  h->nT = nT;
+  h->nnu = nnu;
+  h->iT = iT;
+  h->wT = wT;
+  h->T_ok = ok;
+  h->nu_host.assign(side_nu_host, side_nu_host + nnu);
   cudaFree(cs);
   SynthParams& P = h->P;
   P.n_bands = n_bands;

@@ -46,7 +46,7 @@ __device__ __forceinline__ R r_nan() {
   return (R)__longlong_as_double(0x7ff8000000000000LL);
 }
 
-__device__ __noinline__ void record_out_of_grid(int* flags, int layer, int64_t det, int64_t sample) {
+static __device__ __noinline__ void record_out_of_grid(int* flags, int layer, int64_t det, int64_t sample) {
   atomicOr(&flags[0], 1);
   if (atomicCAS(&flags[6], 0, 1) == 0) {
     flags[1] = layer;

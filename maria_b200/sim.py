@@ -20,20 +20,51 @@ logger = logging.getLogger("maria_b200")
 
 
 class LazyArray:
-    """A (n_det, n_t) array that is evaluated on the device when converted (``np.asarray``) or sliced."""
+    """A (n_det, n_t) array that lives nowhere: ``compute(det0, n)`` evaluates the rows [det0, det0 + n) on the device.
+    Slicing evaluates only the detector range the key touches (``a[100:132]``, ``a[7]``, ``a[idx, ::10]``); converting the
+    whole array (``np.asarray``) evaluates it in detector chunks of at most ``max_chunk_bytes`` on the device."""
 
-    def __init__(self, shape, dtype, compute):
+    def __init__(self, shape, dtype, compute, max_chunk_bytes=2 << 30):
         self.shape, self.dtype, self._compute = tuple(shape), np.dtype(dtype), compute
+        self._rows = max(1, int(max_chunk_bytes // max(1, self.shape[1] * self.dtype.itemsize)))
 
-    def compute_device(self):
-        return self._compute()
+    @property
+    def ndim(self):
+        return 2
+
+    def compute_device(self, det0=0, n=None):
+        return self._compute(det0, self.shape[0] - det0 if n is None else n)
+
+    def _rows_host(self, d0, d1, rest=None):
+        parts = []
+        for a in range(d0, d1, self._rows):
+            blk = self._compute(a, min(self._rows, d1 - a))
+            blk = blk if rest is None else blk[(slice(None),) + rest]
+            parts.append(blk.cpu().numpy())
+        return np.concatenate(parts, axis=0) if parts else np.empty((0,) + self.shape[1:], self.dtype)
 
     def __array__(self, dtype=None, copy=None):
-        a = self._compute().cpu().numpy()
+        a = self._rows_host(0, self.shape[0])
         return a.astype(dtype) if dtype is not None else a
 
     def __getitem__(self, key):
-        return np.asarray(self)[key]
+        key = key if isinstance(key, tuple) else (key,)
+        first, rest = key[0], tuple(key[1:])
+        n = self.shape[0]
+        if isinstance(first, (int, np.integer)):
+            d = int(first) % n
+            return self._rows_host(d, d + 1, rest)[0]
+        if isinstance(first, slice):
+            idx = np.arange(n)[first]
+        else:
+            idx = np.asarray(first)
+            idx = np.nonzero(idx)[0] if idx.dtype == bool else idx % n
+        if len(idx) == 0:
+            return np.empty((0,) + self.shape[1:], self.dtype)[(slice(None),) + rest]
+        d0, d1 = int(idx.min()), int(idx.max()) + 1
+        if (d1 - d0) <= 4 * len(idx):  # one covering range
+            return self._rows_host(d0, d1, rest)[idx - d0]
+        return np.stack([self._rows_host(int(d), int(d) + 1, rest)[0] for d in idx])
 
 
 class Observation:
@@ -74,10 +105,10 @@ class AtmosphereMixin:
         ctx = atm.ctx
         n_det, n_t = obs.instrument.dets.n, len(obs.boresight.t)
 
-        def upsampled():  # linear interp1d to the full rate (:30-37)
-            zp = atm.zenith_pwv_device()
-            out = ctx.empty((n_det, n_t), ctx.torch.float64)
-            ctx.check(ctx.lib.matm_upsample_linear(ctx.h, zp.data_ptr(), n_det, out.data_ptr(), ctx.stream_ptr()))
+        def upsampled(det0, n):  # linear interp1d to the full rate (:30-37), for the detectors [det0, det0 + n)
+            zp = atm.zenith_pwv_device(det0, n)
+            out = ctx.empty((n, n_t), ctx.torch.float64)
+            ctx.check(ctx.lib.matm_upsample_linear(ctx.h, zp.data_ptr(), n, out.data_ptr(), ctx.stream_ptr()))
             return out
 
         obs.zenith_scaled_pwv = LazyArray((n_det, n_t), np.float64, upsampled)
@@ -112,6 +143,7 @@ class Simulation(AtmosphereMixin):
             if obs.atmosphere is not None:
                 t0 = ttime.monotonic()
                 obs.atmosphere.initialize(obs)
+                obs.coords.bind_device(obs.atmosphere)  # obs.coords.az / .el: device slices on demand
                 logger.debug(f"Initialized atmosphere in {ttime.monotonic() - t0:.2f} s")
             self.obs_list.append(obs)
         if det_range is not None:

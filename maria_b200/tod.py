@@ -77,8 +77,13 @@ class TOD:
     @property
     def weight(self):
         if self._weight is None:
-            self._weight = np.ones(self.shape, dtype=np.float64)  # tod.py:68-73
+            # tod.py:68-73: float64 ones of the TOD's shape -- as a zero-stride, read-only view (144 GB at C4 otherwise)
+            self._weight = np.broadcast_to(np.ones((), dtype=np.float64), self.shape)
         return self._weight
+
+    def sample(self, field, dets=slice(None), samples=slice(None)):
+        """``data[field][dets, samples]`` as a host array without copying the whole field off the device."""
+        return self.device_data[field][dets, samples].cpu().numpy()
 
     @property
     def signal_device(self):

@@ -630,3 +630,34 @@ def atmosphere_from_geometry(weather, spectrum, layers, timestep, boresight_t, b
         atm.processes[k] = p
     atm._initialized = True
     return atm
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# consumers of the path's intermediates
+# ---------------------------------------------------------------------------------------------------------------
+def map_pW_per_K_RJ(obs, atmosphere, nu_min_Hz, nu_max_Hz):
+    """maria/sim/map.py:117-133 with band.py:235-255: per band, 1e12 k_B x the trilinear lookup of
+    trapz(passband(nu) exp(-opacity[..., nu]), nu) over spectrum.side_nu in [nu_min, nu_max) at (T0, full-rate
+    zenith_scaled_pwv, full-rate elevation).  (n_det, n_t) float64; ``simulate_atmosphere`` must have run."""
+    dets, sp_ = obs.instrument.dets, atmosphere.spectrum
+    out = np.zeros(obs.zenith_scaled_pwv.shape)
+    nu_mask = (sp_.side_nu >= nu_min_Hz) & (sp_.side_nu < nu_max_Hz)
+    nu = sp_.side_nu[nu_mask]
+    for band in dets.bands:
+        m = dets.mask(band_name=band.name)
+        grid = np.trapezoid(band.passband(nu) * np.exp(-sp_._opacity[..., nu_mask]), x=nu, axis=-1)
+        xi = (atmosphere.weather.temperature[0], obs.zenith_scaled_pwv[m], obs.coords.el[m])
+        out[m] = 1e12 * k_B * rgi_linear(sp_.points[:3], grid, xi, f32=atmosphere.f32)
+    return out
+
+
+def noise_loading_pW(obs, loading_pW, unscaled_noise, nep, nep_per_loading):
+    """maria/sim/noise.py:35-37,60: per band, 1e12 (NEP + NEP_per_loading * sum of the loadings) * unscaled_noise.
+    ``nep`` / ``nep_per_loading``: {band name: W sqrt(s)}."""
+    dets = obs.instrument.dets
+    out = np.zeros(np.shape(loading_pW))
+    for band in dets.bands:
+        m = dets.mask(band_name=band.name)
+        total = nep[band.name] + nep_per_loading[band.name] * np.asarray(loading_pW, dtype=np.float64)[m]
+        out[m] = 1e12 * total * np.asarray(unscaled_noise, dtype=np.float64)[m]
+    return out
