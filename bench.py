@@ -46,7 +46,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the sequential / strong / parity-probe blocks")
-    ap.add_argument("--depth", type=int, default=3, help="realisations whose AR chains are in flight underneath the synthesis")
+    ap.add_argument("--depth", type=int, default=None,
+                    help="realisations whose AR chains are in flight underneath the synthesis (default 3; c5: as many as the "
+                         "~300 ms six-hour chains need to hide behind the per-rank synthesis)")
     ap.add_argument("--chunk-mib", type=int, default=None, help="scratch per detector chunk of the two-kernel synthesis [MiB]")
     ap.add_argument("--chunk-serial", action="store_true", help="run the detector chunks of one synthesis on one stream")
     ap.add_argument("--kernel-times", action="store_true", help="bracket every launch of the two synthesis kernels with events")
@@ -393,20 +395,26 @@ def strong_block(args, torch, dist, rank, world, device, steps, n1_value):
     stream, underneath the previous realisation's synthesis (SURVEY.md section 8e option B)."""
     from maria_b200 import configs, sharding
 
-    cfg = configs.c4_atlast(n_det=args.n_det, duration=args.duration or 3600.0, sample_rate=args.sample_rate, n_groups=1)
+    # the N = 1 focal plane (n_det detectors = n_det / 2 dichroic pixels in the same 2-degree field), its detectors emitted
+    # in `world` blocks that each hold both bands of their pixels (maria sorts detectors by band inside an array; a shard
+    # that kept only one band of every pixel would repeat every line of sight on two ranks)
+    per = (args.n_det // world) // 64 * 64
+    cfg = configs.c4_atlast(n_det=per, duration=args.duration or 3600.0, sample_rate=args.sample_rate, n_groups=world)
     n, n_t = cfg["instrument"].dets.n, len(cfg["plan"].time)
-    det0, cnt = sharding.detector_range(n, rank, world)
-    sim = make_sim(cfg, (det0, cnt), device, max(1, args.depth), exchange=True)
+    det0, cnt = rank * per, per
+    # a realisation cannot finish faster than its longest AR chain (~40 ms): enough realisations in flight to cover it
+    depth = int(min(16, max(args.depth, np.ceil(45.0 * world / 27.0) + 1)))
+    sim = make_sim(cfg, (det0, cnt), device, depth, exchange=True)
     atm = sim.obs_list[0].atmosphere
     atm.set_gain(np.exp(cfg["instrument"].dets.gain_error * np.random.standard_normal(size=n)))
     out = atm.ctx.empty((cnt, n_t))
     stepper = Stepper(torch, sim, out, overlap=True)
-    r = timed_run(torch, dist, world, device, stepper, steps, 3)
+    r = timed_run(torch, dist, world, device, stepper, steps, max(3, depth))
     stepper.drain()
     value = n * n_t / (r["ms_per_step"] * 1e-3)
     layer_bytes = sum(4 * p.n_extrusion * p.n_cross_section for p in atm.processes.values())
     res = {"value": value, "unit": "detector-samples/s", "ms_per_step": r["ms_per_step"], "synth_ms": r["synth_ms"],
-           "n_det_total": n, "n_det_per_gpu": cnt, "steps": steps, "layer_exchange": "one torch.distributed broadcast (NCCL) per "
+           "n_det_total": n, "n_det_per_gpu": cnt, "steps": steps, "pipeline_depth": depth, "layer_exchange": "one torch.distributed broadcast (NCCL) per "
            "layer from rank (process index mod N), on the process's stream", "nccl_bytes_per_step_per_rank": layer_bytes,
            "generate_and_exchange_ms": r["gen_ms"], "status": r["status"],
            "efficiency_vs_n1": (value / (world * n1_value)) if n1_value else None,
@@ -500,6 +508,11 @@ def run_e2e(args, torch, dist, world, local, sim, cfg, gain, barrier):
 def run_b200(args):
     import torch
     import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.depth is None:
+        # C5's longest layer is a ~300 ms chain (223 k dependent steps); one rank synthesises its shard in ~200 / N ms
+        args.depth = 3 if args.config != "c5" else int(min(16, max(3, np.ceil(300.0 * world / 200.0) + 2)))
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -613,7 +626,7 @@ def run_b200(args):
                     n1 = float(j["value"])
             except Exception:
                 pass
-            extras["strong"] = strong_block(args, torch, dist, rank, world, local, min(args.steps, 5), n1)
+            extras["strong"] = strong_block(args, torch, dist, rank, world, local, max(args.steps, 10), n1)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -76,6 +76,11 @@ def load(build_if_missing=True):
         if not build_if_missing:
             raise RuntimeError(f"{path} is missing: run `python -m maria_b200._build`")
         _build.build()
+    elif _build.is_stale():
+        import logging
+
+        logging.getLogger("maria_b200").warning(f"{path} is older than its sources: run `python -m maria_b200._build` "
+                                                "(measurements would describe the old kernels)")
     lib = C.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported

@@ -367,8 +367,10 @@ class Atmosphere:
         self.ctx = DeviceContext(self.device, self.precision)
         self._bind_scan_and_detectors(obs, None)
         self.set_bands(obs.instrument.dets)
-        for p in self.processes.values():
-            p.bind(self.ctx, self.pipeline_depth)
+        rank, world = self._rank_world()
+        for k, p in self.processes.items():
+            # under layer_exchange a rank runs only its own processes: the others need no BUFFER / Z on this GPU
+            p.bind(self.ctx, self.pipeline_depth if k % world == rank else 0)
         self._pending_slots, self._issued = [], 0
         self._layer_sets = [{}, {}]   # two sets of smoothed-layer buffers: the sampler reads one, the next is written
         self._layer_cur = 0

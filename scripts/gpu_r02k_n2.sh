@@ -1,4 +1,4 @@
-TAG=r02k
+TAG=r02n
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_gpu_multirank.py -q > gpurun_out/pytest_multirank_n2_$TAG.log 2>&1; tail -3 gpurun_out/pytest_multirank_n2_$TAG.log
 timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 2 --steps 6 --warmup 3 > gpurun_out/bench_n2_$TAG.json 2> gpurun_out/bench_n2_$TAG.err
