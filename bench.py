@@ -224,6 +224,8 @@ def run_reference(args):
     # K + W steps must end within a few minutes: the sample shrinks with the number of steps (~0.075 s per detector + 2 s)
     total = args.steps + min(args.warmup, 1)
     n_dets = args.cpu_dets if total <= 6 else (128 if total <= 12 else 64)
+    if args.config in ("c1", "c2", "c3"):  # the reference's own CPU-runnable cases: the whole configuration, not a sample
+        n_dets = cfg["instrument"].dets.n
     cpu, wall = cpu_baseline(cfg, atm, n_dets, steps=args.steps, warmup=min(args.warmup, 1))
     line = {
         "impl": "reference", "metric": "atmospheric TOD detector-samples/sec", "value": cpu["value"], "unit": "detector-samples/s",
@@ -631,7 +633,7 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         torch.cuda.empty_cache()
-        cpu, _ = cpu_baseline(cfg, atm, args.cpu_dets)
+        cpu, _ = cpu_baseline(cfg, atm, cfg["instrument"].dets.n if args.config in ("c1", "c2", "c3") else args.cpu_dets)
     if rank == 0:
         depth = atm.pipeline_depth
         line = {
