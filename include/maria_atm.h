@@ -144,6 +144,21 @@ int matm_set_tuning(matm_handle* h, int chunk_mib, int overlap);
 int matm_set_timing(matm_handle* h, int enable);
 int matm_get_timing(matm_handle* h, double* loading_ms, double* eval_ms, int64_t* n_chunks);
 
+/* Allocation-free variant of matm_synthesize for float32 handles.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same kernels, same detector order and bit-identical output to matm_synthesize, but the knot-value scratch
+ * (ceil(n_det / 32) tiles x n_t_atm knots x 128 B) lives in one file-scope `static __device__` array of
+ * MATM_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; the call makes no cudaMalloc / cudaFree /
+ * stream or event creation.  Returns MATM_ERR_ARG (with the sizes in matm_last_error) when the scratch needed exceeds the
+ * maximum -- split the detector range -- for float64 handles, and when the processing order of (det0, n_det) is not cached
+ * yet: call matm_synthesize once for the same range at set-up (that call allocates the order), outside any capture; the first
+ * call on a device also resolves the array's device address (cudaGetSymbolAddress).  Every call shares the array, which keeps
+ * the last call's contents (nothing needs to start at zero: the loading kernel overwrites every element the evaluation kernel
+ * reads); calls that overlap on the GPU RACE -- issue them on one stream or order them yourself. */
+#define MATM_NOALLOC_SCRATCH_BYTES (32u << 20)
+int matm_synthesize_noalloc(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, int units, int apply_gain,
+                            void* stream);
+
 /* Same, delivering into HOST memory (pinned or pageable): detector-chunked, device->host copies overlapped with
  * the kernels of the next chunk.  Synchronises before returning. */
 int matm_synthesize_host(matm_handle* h, int64_t det0, int64_t n_det, void* out_host, int units, int apply_gain);

@@ -50,6 +50,7 @@ SIGNATURES = {
     "matm_set_timing": (C.c_int, [vp, C.c_int]),
     "matm_get_timing": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "matm_synthesize_host": (C.c_int, [vp, C.c_int64, C.c_int64, vp, C.c_int, C.c_int]),
+    "matm_synthesize_noalloc": (C.c_int, [vp, C.c_int64, C.c_int64, vp, C.c_int, C.c_int, vp]),
     "matm_calibrate": (C.c_int, [vp, C.c_int64, C.c_int64, vp, vp, C.c_int, vp]),
     "matm_transmission": (C.c_int, [vp, C.c_int64, C.c_int64, C.c_double, C.c_double, vp, vp]),
     "matm_noise_scale": (C.c_int, [vp, C.c_int64, C.c_int64, vp, vp, c_dp, c_dp, vp, vp]),

@@ -1,5 +1,7 @@
 // The detector x time stages: a6/a7/a9 (line-of-sight sampling), a10 (linear upsample), and the fused
 // a6..a14 synthesis kernel (sampling -> emission lookup -> cubic not-a-knot upsample -> gain -> pW->K_RJ).
+#include <mutex>
+
 #include "matm_synth.cuh"
 #include "matm_synth_f32.cuh"
 
@@ -485,5 +487,88 @@ extern "C" int matm_synthesize_host(matm_handle* h, int64_t det0, int64_t n_det,
   }
   MATM_CUDA(h, cudaStreamSynchronize(h->stage_stream[0]));
   MATM_CUDA(h, cudaStreamSynchronize(h->stage_stream[1]));
+  return MATM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the float synthesis (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  Same two kernels, same detector order, same results as matm_synthesize; the knot-value scratch
+// yk[tile][n_t_atm][32] lives in ONE file-scope device array of MATM_NOALLOC_SCRATCH_BYTES that every GPU loading
+// the library holds until exit.  Every call shares it: calls that overlap on the GPU race (the caller serialises
+// them, e.g. by issuing them on one stream).  Nothing has to start at zero: loading_f32_kernel writes all 32 slots
+// of every knot row of every tile of the launch (idle lanes of a partial tile shadow the last detector) before
+// the evaluation kernel of the same stream reads them, so the previous call's contents are never observed.
+// ---------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_noalloc_yk[MATM_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+#define MATM_NOALLOC_MAX_DEVICES 64
+static float* g_noalloc_yk_addr[MATM_NOALLOC_MAX_DEVICES];  // device address of g_noalloc_yk, per device
+static std::mutex g_noalloc_mutex;
+
+// In host code the NAME g_noalloc_yk is a host-side stand-in, not a device address: the address a kernel can use is
+// looked up once per device, with that device current (first call on the device = its set-up), and cached.
+static int noalloc_scratch(matm_handle* h, float** out) {
+  if (h->device < 0 || h->device >= MATM_NOALLOC_MAX_DEVICES) MATM_FAIL_ARG(h, "matm_synthesize_noalloc: device index out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_yk_addr[h->device]) {
+    void* p = nullptr;
+    MATM_CUDA(h, cudaGetSymbolAddress(&p, g_noalloc_yk));
+    if (!p) MATM_FAIL_ARG(h, "matm_synthesize_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_yk_addr[h->device] = static_cast<float*>(p);
+  }
+  *out = g_noalloc_yk_addr[h->device];
+  return MATM_OK;
+}
+
+extern "C" int matm_synthesize_noalloc(matm_handle* h, int64_t det0, int64_t n_det, void* out_dev, int units, int apply_gain,
+                                       void* stream) {
+  MATM_CHECK_HANDLE(h);
+  if (matm_set_device(h)) return MATM_ERR_CUDA;
+  if (h->dtype != MATM_F32) MATM_FAIL_ARG(h, "matm_synthesize_noalloc: float32 handles only (the float64 kernel has no scratch)");
+  int rc = check_ready(h, true, det0, n_det);
+  if (rc) return rc;
+  if (!out_dev || (units != MATM_UNITS_PW && units != MATM_UNITS_KRJ)) MATM_FAIL_ARG(h, "matm_synthesize_noalloc: bad arguments");
+  const SynthParams& P = h->P;
+  const int n = P.n_t_atm;
+  if (n < 4) MATM_FAIL_ARG(h, "cubic upsample needs at least 4 atmosphere-rate samples (scipy interp1d kind='cubic')");
+  const int64_t n_tiles = (n_det + F32_DT - 1) / F32_DT;
+  const size_t need = (size_t)n_tiles * (size_t)n * F32_DT * sizeof(float);
+  if (need > (size_t)MATM_NOALLOC_SCRATCH_BYTES) {
+    h->err = "matm_synthesize_noalloc: scratch of " + std::to_string(need) + " B (ceil(n_det / 32) = " + std::to_string(n_tiles) +
+             " tiles x n_t_atm = " + std::to_string(n) + " knots x 128 B) exceeds the static maximum of " +
+             std::to_string((size_t)MATM_NOALLOC_SCRATCH_BYTES) + " B; split the detector range or use matm_synthesize";
+    return MATM_ERR_ARG;
+  }
+  // the processing order of the range is built (and allocated) by matm_synthesize; here it is only looked up
+  auto it = h->det_order.find(std::make_pair(det0, n_det));
+  if (it == h->det_order.end())
+    MATM_FAIL_ARG(h, "matm_synthesize_noalloc: no cached processing order for this detector range; call matm_synthesize once for "
+                     "the same (det0, n_det) at set-up (it allocates the order), then this entry point allocates nothing");
+  const int32_t* order = it->second.order;
+  const uint8_t* tile_m = it->second.tile_m;
+  float* yk = nullptr;
+  rc = noalloc_scratch(h, &yk);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n_kb = (n + LD_KA - 1) / LD_KA, n_tt = (n - 1 + F32_KT - 1) / F32_KT;
+  if (n_tiles * (int64_t)max(n_kb, n_tt) > INT32_MAX) MATM_FAIL_ARG(h, "matm_synthesize_noalloc: too many tiles");
+  const size_t smem = synth_f32_smem();
+  const bool fast = h->min_samples_per_interval >= 4 && P.n_t < ((int64_t)1 << 30) && n_det < ((int64_t)1 << 31);
+  auto eval_kernel = fast ? synth_eval_f32_kernel : synth_eval_general_f32_kernel;
+  MATM_CUDA(h, cudaFuncSetAttribute(eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t smem_a = (size_t)P.n_layers * LD_KA * sizeof(int4);
+  MATM_CUDA(h, cudaFuncSetAttribute(loading_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_a));
+  {  // pair-expanded copy of the smoothed layers (buffers allocated by matm_set_layers)
+    int max_cells = 1;
+    for (int l = 0; l < P.n_layers; l++) max_cells = max(max_cells, P.layers[l].n_ext * P.layers[l].n_cs);
+    dim3 grid((unsigned)min(4 * h->sm_count, (max_cells + 255) / 256), (unsigned)P.n_layers);
+    expand_layers_kernel<<<grid, 256, 0, st>>>(P);
+    MATM_LAUNCHED(h);
+  }
+  loading_f32_kernel<<<(unsigned)(n_tiles * n_kb), LD_THREADS, smem_a, st>>>(P, order, tile_m, 0, n_det, yk, apply_gain);
+  MATM_LAUNCHED(h);
+  eval_kernel<<<(unsigned)(n_tiles * n_tt), F32_THREADS, smem, st>>>(P, order, 0, det0, n_det, yk, (float*)out_dev, units);
+  MATM_LAUNCHED(h);
   return MATM_OK;
 }
