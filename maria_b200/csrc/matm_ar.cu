@@ -223,6 +223,25 @@ __device__ __forceinline__ void st_async_f64(uint32_t remote_addr, double v, uin
                "r"(remote_bar)
                : "memory");
 }
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_f64(uint32_t addr, double v) {
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+// the same under a predicate inside the instruction stream: no branch, no reconvergence point around the store
+__device__ __forceinline__ void st_async_f64_if(bool p, uint32_t remote_addr, double v, uint32_t remote_bar) {
+  asm volatile(
+      "{\n"
+      ".reg .pred q;\n"
+      "setp.ne.u32 q, %3, 0;\n"
+      "@q st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];\n"
+      "}\n" ::"r"(remote_addr),
+      "d"(v), "r"(remote_bar), "r"((uint32_t)p)
+      : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
@@ -234,28 +253,60 @@ __device__ __forceinline__ void mbar_arm(uint32_t bar, uint32_t bytes) {
 }
 // wait for the phase of the given parity; data written by st.async of other CTAs is visible afterwards.  A wait that
 // never ends is a bug in the byte accounting: trap instead of hanging the device.
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"  // transaction barrier: the bytes it counted are visible
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done;
+}
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
+  // try_wait suspends the warp in hardware until the phase completes or a time limit passes: the first attempt almost always
+  // succeeds; the counting loop is the rare path
+  if (mbar_try_wait(bar, parity)) return;
   int spins = 0;
-  while (!done) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"  // transaction barrier: the bytes it counted are visible
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (!done && ++spins > (1 << 22)) __trap();
-  }
+  while (!mbar_try_wait(bar, parity))
+    if (++spins > (1 << 22)) __trap();
 }
 
+#ifdef MATM_AR_TRACE
+// Diagnostic build only (-DMATM_AR_TRACE, scripts/chain_trace.py): SM clocks at the phase boundaries of 128 steps of the
+// steady state, for warps 0 and 3 of every CTA.
+static __device__ long long g_ar_trace[16][128][6];
+__device__ __forceinline__ long long ar_clock_after(double x) {
+  long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) : "d"(x) : "memory");
+  return t;
+}
+#define AR_TRACE(k, dep)                                                   \
+  if (tr_on && i < tr_hi && i >= tr_hi - 128) g_ar_trace[tr_slot][i & 127][k] = ar_clock_after(dep)
+extern "C" int matm_debug_ar_trace(long long* out_host) {
+  return cudaMemcpyFromSymbol(out_host, g_ar_trace, sizeof(g_ar_trace)) == cudaSuccess ? 0 : 1;
+}
+#else
+#define AR_TRACE(k, dep)
+#endif
+
+// the phase (step & 3) of a step: a compile-time constant in the unrolled steady state, a run-time value elsewhere
+template <int V>
+struct PhaseConst {};
+template <int V>
+__device__ __forceinline__ constexpr int phase_value(PhaseConst<V>) { return V; }
+__device__ __forceinline__ constexpr int phase_value(int v) { return v; }
+
 // MC >= 0: the LATE part is registers [0, 4 MC), fixed at compile time; CL > 0: the cluster size, fixed at compile time
-template <int L, int MP, int MC = -1, int CL = 0>
-__global__ void __launch_bounds__(AR_THREADS, 1)
+// NT: threads per CTA.  512 = 128 registers per thread and up to 16 warps of rows per SM (the smallest cluster); 256 = 255
+// registers, 8 warps (two per scheduler): fewer rows per SM, more CTAs per cluster, a shorter step.
+template <int L, int MP, int MC = -1, int CL = 0, int NT = AR_THREADS>
+__global__ void __launch_bounds__(NT, 1)
     ar_chain_v4_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
-                       double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl) {
+                       double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl, int n_ring, int fence_mask) {
   constexpr int RPW = 32 / L;  // rows per warp
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int gs = L * MP;                                     // padded length of one gather vector
@@ -264,6 +315,8 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   int* cnt = reinterpret_cast<int*>(bars + 8);               // [4]: near samples of offset 1, 2, 3
   int* pos = cnt + 4;                                        // [3][n_cs]: position of column c among the samples of offset 1, 2, 3
   const int n_far = n_sample - n_near;
+  int* roff = pos + 3 * n_cs;                                // [n_ring + 1]: start of the delay line of far sample f
+  double* ring = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(roff + n_ring + 1) + 15) & ~(uintptr_t)15);
   int cta = 0;
   if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
   const int rpc = (n_cs + cl - 1) / cl;
@@ -277,32 +330,75 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   const uint32_t G_s = smem_u32(G), bars_s = smem_u32(bars);
 
   // ---- set-up: A into registers, G zeroed, inverse stencil maps, sample counts per offset ----
+  // lane `sub` holds the sample PAIRS 2 (sub + L q), 2 (sub + L q) + 1 in registers 2 q, 2 q + 1: one 16-byte shared-memory
+  // load feeds two FMAs, and the L lanes of a row read 16 L contiguous bytes (a full 128-byte wavefront at L = 8)
+  static_assert(MP % 4 == 0, "registers are consumed in groups of four (two 16-byte loads)");
   double a[MP];
 #pragma unroll
   for (int m = 0; m < MP; m++) {
-    const int s = sub + L * m;
+    const int s = 2 * (sub + L * (m / 2)) + (m & 1);
     a[m] = (has_row && s < n_sample) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
   }
-  for (int e = tid; e < 4 * gs; e += AR_THREADS) G[e] = 0.0;
-  for (int e = tid; e < 3 * n_cs; e += AR_THREADS) pos[e] = -1;
+  for (int e = tid; e < 4 * gs; e += NT) G[e] = 0.0;
+  for (int e = tid; e < 3 * n_cs; e += NT) pos[e] = -1;
   if (tid < 4) cnt[tid] = 0;
   if (tid == 0) {
     for (int b = 0; b < 8; b++) mbar_init(bars + b, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  for (int s = tid; s < n_near; s += AR_THREADS) {
+  for (int s = tid; s < n_near; s += NT) {
     pos[esi[s] * n_cs + csi[s]] = s;  // offset = esi + 1 in 1..3
     atomicAdd(&cnt[esi[s]], 1);
   }
   int foff[2];
 #pragma unroll
   for (int q = 0; q < 2; q++) {
-    const int f = tid + q * AR_THREADS;
+    const int f = tid + q * NT;
     foff[q] = f < n_far ? (esi[n_near + f] + 1) * n_cs + csi[n_near + f] : -1;
   }
   __syncthreads();
   const int n1 = cnt[0], n2 = cnt[1], n3 = cnt[2];
+  // ---- delay lines of the far samples ------------------------------------------------------------------------------
+  // A far sample (offset d >= 4, column c) of step s is the value (s + d, c).  Reading it back from BUFFER in global memory
+  // is only safe once the producer's store is known to be visible; a store followed by st.async carries no such guarantee
+  // (measured: with 0.5 us steps and a synthesis kernel loading the memory system, the offset-5 samples, read one step after
+  // they were produced, came back stale).  So the first n_ring far samples (the host checks that they include every offset
+  // below 64) never touch global memory: every CTA receives the whole row i + 1 in the LATE part of its gather vector of
+  // step i, the thread that owns far sample f copies (i + 1, c_f) from there into a private ring of d_f - 3 entries and
+  // takes out (i - 2 + d_f, c_f), stored d_f - 3 steps earlier, which it sends into the vector of step i - 2.  The remaining
+  // samples (offset >= 70, i.e. read >= 66 steps after they were produced) keep the global path, ordered by a
+  // __threadfence() of every thread every (fence_mask + 1) <= 64 steps: the store of row j is followed by a fence at most 63
+  // steps later, the fence by the thread's next st.async, and the reader has waited on a barrier those bytes completed.
+  if (tid == 0) {
+    int used = 0;
+    for (int f = 0; f < n_ring; f++) {
+      roff[f] = used;
+      used += esi[n_near + f] + 1 - 3;
+    }
+    roff[n_ring] = used;
+  }
+  __syncthreads();
+  for (int f = 0; f < n_ring; f++) {
+    const int lr = esi[n_near + f] + 1 - 3, c = csi[n_near + f], ro = roff[f];
+    for (int k = tid; k < lr; k += NT) {  // rows i_top + 2 ... i_top - 2 + d: the initial noise, written by an earlier kernel
+      const int row = i_top + 2 + k;
+      ring[ro + row % lr] = buffer[(size_t)row * n_cs + c];
+    }
+  }
+  uint32_t ring_p[2], ring_lo[2], ring_hi[2], ring_src[2];
+#pragma unroll
+  for (int q = 0; q < 2; q++) {
+    const int f = tid + q * NT;
+    ring_p[q] = ring_lo[q] = ring_hi[q] = ring_src[q] = 0u;
+    if (f < n_ring) {
+      const int d = esi[n_near + f] + 1, lr = d - 3;
+      ring_lo[q] = smem_u32(ring + roff[f]);
+      ring_hi[q] = ring_lo[q] + 8u * (lr - 1);
+      ring_p[q] = ring_lo[q] + 8u * ((i_top - 2 + d) % lr);
+      ring_src[q] = 8u * pos[csi[n_near + f]];  // where the row just completed holds column c_f (offset-1 sample of c_f)
+    }
+  }
   // registers [0, mcrit) hold every offset-1 sample (the samples are sorted by offset): the part of the dot product that
   // has to wait for the row just produced; the rest is computed one step ahead
   // (with MC given by the host from n_cs >= n1, the unrolled groups carry no branch and their loads are batched)
@@ -315,13 +411,16 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   }
   // With the cluster size known at compile time the 3 CL destinations of a value are spread over the L lanes of its row
   // (after the butterfly every lane holds the sum): lane `sub` sends to (CTA t / 3, gather vector of step i - 1 - t % 3)
-  // for t = sub and t = sub + L.
-  constexpr bool SPREAD = CL > 0 && 3 * CL <= 2 * L;
-  uint32_t pubd[2] = {0, 0}, pubb[2] = {0, 0};
-  int pubk[2] = {0, 0};
+  // for t = sub, sub + L, ... < 3 CL.
+  constexpr int NJ = CL > 0 ? (3 * CL + L - 1) / L : 1;  // destinations per lane
+  constexpr bool SPREAD = CL > 0 && NJ <= 3;
+  uint32_t pubd[NJ], pubb[NJ];
+  int pubk[NJ];
+#pragma unroll
+  for (int j = 0; j < NJ; j++) pubd[j] = pubb[j] = 0u, pubk[j] = 0;
   if (SPREAD) {
 #pragma unroll
-    for (int j = 0; j < 2; j++) {
+    for (int j = 0; j < NJ; j++) {
       const int t = sub + j * L, c = min(t / 3, cl - 1), k = t % 3 + 1;
       const int pk = (has_row && t < 3 * cl) ? pos[(k - 1) * n_cs + row0 + r] : -1;
       pubk[j] = pk >= 0 ? k : 0;
@@ -330,7 +429,7 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
     }
   }
   // ---- prologue: the initial-noise rows i_top+1 .. i_top+3 feed steps i_top, i_top-1, i_top-2 ----
-  for (int e = tid; e < 3 * n_near; e += AR_THREADS) {
+  for (int e = tid; e < 3 * n_near; e += NT) {
     const int k = e / n_near, s = e % n_near;  // step i_top - k, near sample s
     const int off = esi[s] + 1;
     if (off > k && i_top - k >= 0)
@@ -339,7 +438,7 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
 #pragma unroll
   for (int q = 0; q < 2; q++)
     if (foff[q] >= 0) {
-      const int f = n_near + tid + q * AR_THREADS;
+      const int f = n_near + tid + q * NT;
       G[(i_top & 3) * gs + f] = buffer[(size_t)i_top * n_cs + foff[q]];
       if (i_top >= 1) G[((i_top - 1) & 3) * gs + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
     }
@@ -374,16 +473,17 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   cluster_barrier();
 
   // the EARLY part of the dot product of step j: registers [mcrit, MP)
-  auto early_part = [&](const int j) -> double {
-    const double* g = G + (j & 3) * gs + sub;
+  auto early_part = [&](const int ph) -> double {  // ph = (step & 3): the gather vector of that step
+    const double2* g = reinterpret_cast<const double2*>(G + ph * gs) + sub;
     double e0 = 0.0, e1 = 0.0, e2 = 0.0, e3 = 0.0;
 #pragma unroll
     for (int m = 0; m < MP; m += 4)
       if (MC >= 0 ? (m >= 4 * MC) : (m >= mcrit)) {
-        e0 = fma(a[m], g[L * m], e0);
-        if (m + 1 < MP) e1 = fma(a[m + 1], g[L * (m + 1)], e1);
-        if (m + 2 < MP) e2 = fma(a[m + 2], g[L * (m + 2)], e2);
-        if (m + 3 < MP) e3 = fma(a[m + 3], g[L * (m + 3)], e3);
+        const double2 v0 = g[L * (m / 2)], v1 = g[L * (m / 2 + 1)];
+        e0 = fma(a[m], v0.x, e0);
+        e1 = fma(a[m + 1], v0.y, e1);
+        e2 = fma(a[m + 2], v1.x, e2);
+        e3 = fma(a[m + 3], v1.y, e3);
       }
     return (e0 + e1) + (e2 + e3);
   };
@@ -391,47 +491,63 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
   const bool active = (warp * RPW < rows) || (warp * 32 < n_far);
   double pre = 0.0;
   if (active) {
-    pre = early_part(i_top);
+    pre = early_part(i_top & 3);
+    // this CTA's own window of the cluster's shared address space (the far samples and their barrier stay at home)
+    const uint32_t bars_self = mapa_u32(bars_s, cta);
+    const uint32_t far_self = mapa_u32(G_s, cta) + 8u * (n_near + tid);
 
     // GD = false: the steady state (i >= 5), where every "does that step exist" test below is true
-    auto step = [&](auto guard, const int i, double(&fs)[2], double& bz) {
+    // element offsets inside BUFFER fit 31 bits (3 n_ext n_cs <= INT32_MAX is checked by the host): 32-bit index arithmetic
+    const int myrow = row0 + r;
+#ifdef MATM_AR_TRACE
+    const bool tr_on = lane == 0 && (warp == 0 || warp == 3) && cta < 8;
+    const int tr_slot = cta * 2 + (warp == 3), tr_hi = i_top - 4096;
+#endif
+    // `phase` = i & 3, the gather vector of step i: a compile-time constant in the steady state (the loop below is unrolled
+    // by four), so that every shared-memory address of the step is a register plus an immediate
+    auto step = [&](auto guard, auto phase, const int i, double(&fs)[2], double& bz) {
       constexpr bool GD = decltype(guard)::value;
+      const int PH = phase_value(phase), PH1 = (PH + 3) & 3, PH2 = (PH + 2) & 3, PH3 = (PH + 1) & 3;  // steps i, i - 1, i - 2, i - 3
       const int ncl = CL > 0 ? CL : cl;
       const uint32_t par = ((i_top - i) >> 2) & 1;
       // (1) the row just produced has landed in G[i]
-      mbar_wait_cluster(bars_s + 8 * (i & 3), par);
-      if (tid == 0 && (!GD || i >= 4)) mbar_arm(bars_s + 8 * (i & 3), late_full);
+      AR_TRACE(0, pre);
+      mbar_wait_cluster(bars_s + 8 * PH, par);
+      AR_TRACE(1, pre);
+      if (tid == 0 && (!GD || i >= 4)) mbar_arm(bars_s + 8 * PH, late_full);
       // (2) the LATE part of the dot product
-      const double* g = G + (i & 3) * gs + sub;
+      const double2* g = reinterpret_cast<const double2*>(G + PH * gs) + sub;
       double acc0 = pre, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
 #pragma unroll
       for (int m = 0; m < MP; m += 4)
         if (MC >= 0 ? (m < 4 * MC) : (m < mcrit)) {
-          acc0 = fma(a[m], g[L * m], acc0);
-          if (m + 1 < MP) acc1 = fma(a[m + 1], g[L * (m + 1)], acc1);
-          if (m + 2 < MP) acc2 = fma(a[m + 2], g[L * (m + 2)], acc2);
-          if (m + 3 < MP) acc3 = fma(a[m + 3], g[L * (m + 3)], acc3);
+          const double2 v0 = g[L * (m / 2)], v1 = g[L * (m / 2 + 1)];
+          acc0 = fma(a[m], v0.x, acc0);
+          acc1 = fma(a[m + 1], v0.y, acc1);
+          acc2 = fma(a[m + 2], v1.x, acc2);
+          acc3 = fma(a[m + 3], v1.y, acc3);
         }
       double acc = (acc0 + acc1) + (acc2 + acc3);
+      AR_TRACE(2, acc);
 #pragma unroll
       for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      AR_TRACE(3, acc);
       // (3) publish row r of step i into the gather vectors of steps i-1, i-2, i-3 of every CTA, and to global memory
       if (SPREAD) {
         const double v = bz + acc;
-        if (has_row && sub == 0) buffer[(size_t)i * n_cs + row0 + r] = v;  // read again (far samples) three steps from now at the earliest
+        if (has_row && sub == 0) buffer[(uint32_t)(i * n_cs + myrow)] = v;  // read again (far samples) three steps from now at the earliest
 #pragma unroll
-        for (int j = 0; j < 2; j++) {
-          if (j == 1 && 3 * CL <= L) break;
-          const int bsel = (i - pubk[j]) & 3;
-          if (pubk[j] != 0 && (!GD || i >= pubk[j])) st_async_f64(pubd[j] + 8u * (bsel * gs), v, pubb[j] + 8u * bsel);
+        for (int j = 0; j < NJ; j++) {
+          const int bsel = (PH - pubk[j]) & 3;
+          st_async_f64_if(pubk[j] != 0 && (!GD || i >= pubk[j]), pubd[j] + 8u * (bsel * gs), v, pubb[j] + 8u * bsel);
         }
       } else
       if (has_row && sub == 0) {
         const double v = bz + acc;
-        const uint32_t d1 = G_s + 8u * (((i - 1) & 3) * gs + p1), b1 = bars_s + 8u * ((i - 1) & 3);
-        const uint32_t d2 = G_s + 8u * (((i - 2) & 3) * gs + p2), b2 = bars_s + 8u * (4 + ((i - 2) & 3));
-        const uint32_t d3 = G_s + 8u * (((i - 3) & 3) * gs + p3), b3 = bars_s + 8u * (4 + ((i - 3) & 3));
-        buffer[(size_t)i * n_cs + row0 + r] = v;  // read again (far samples) no sooner than three steps from now
+        const uint32_t d1 = G_s + 8u * (PH1 * gs + p1), b1 = bars_s + 8u * PH1;
+        const uint32_t d2 = G_s + 8u * (PH2 * gs + p2), b2 = bars_s + 8u * (4 + PH2);
+        const uint32_t d3 = G_s + 8u * (PH3 * gs + p3), b3 = bars_s + 8u * (4 + PH3);
+        buffer[(uint32_t)(i * n_cs + myrow)] = v;  // read again (far samples) no sooner than three steps from now
 #pragma unroll
         for (int c = 0; c < (CL > 0 ? CL : 8); c++) {
           if (c >= ncl) break;
@@ -440,61 +556,82 @@ __global__ void __launch_bounds__(AR_THREADS, 1)
           if (p3 >= 0 && (!GD || i >= 3)) st_async_f64(mapa_u32(d3, c), v, mapa_u32(b3, c));
         }
       }
+      AR_TRACE(4, acc);
       // (4) off the critical path: send the far values of step i - 2 (in flight since step i + 4), re-issue the set for
       //     step i - 4 (rows >= i + 1, complete: their LATE barrier was passed above), re-issue B z for step i - 2
-      if (!GD || i >= 2) {
-        const uint32_t be = mapa_u32(bars_s + 8u * (4 + ((i - 2) & 3)), cta);
+      {
+        const uint32_t be = bars_self + 8u * (4 + PH2);
 #pragma unroll
         for (int q = 0; q < 2; q++)
-          if (foff[q] >= 0)
-            st_async_f64(mapa_u32(G_s + 8u * (((i - 2) & 3) * gs + n_near + tid + q * AR_THREADS), cta), fs[q], be);
+          if (foff[q] >= 0) {
+            double v = fs[q];
+            if (ring_hi[q] != 0u) {  // delay line: take (i - 2 + d, c) out, put (i + 1, c) in its place
+              const double vnew = lds_f64(G_s + 8u * (PH * gs) + ring_src[q]);
+              v = lds_f64(ring_p[q]);
+              sts_f64(ring_p[q], vnew);
+              ring_p[q] = ring_p[q] == ring_lo[q] ? ring_hi[q] : ring_p[q] - 8u;
+            }
+            if (!GD || i >= 2) st_async_f64(far_self + 8u * (PH2 * gs + q * NT), v, be);
+            if (ring_hi[q] == 0u && (!GD || i >= 4)) fs[q] = __ldcg(buffer + (uint32_t)((i - 4) * n_cs + foff[q]));
+          }
       }
-      if (!GD || i >= 4) {
-#pragma unroll
-        for (int q = 0; q < 2; q++)
-          if (foff[q] >= 0) fs[q] = __ldcg(buffer + (size_t)(i - 4) * n_cs + foff[q]);
-      }
-      if ((!GD || i >= 2) && has_row) bz = __ldcg(buffer + (size_t)(i - 2) * n_cs + row0 + r);
+      if (fence_mask >= 0 && (i & fence_mask) == 0) __threadfence();
+      if ((!GD || i >= 2) && has_row) bz = __ldcg(buffer + (uint32_t)((i - 2) * n_cs + myrow));
       // (5) the EARLY part of step i - 1, while the row of step i is on its way
       if (!GD || i >= 1) {
         const uint32_t pe = ((i_top - (i - 1)) >> 2) & 1;
-        mbar_wait_cluster(bars_s + 8 * (4 + ((i - 1) & 3)), pe);
-        if (tid == 0 && (!GD || i - 1 >= 4)) mbar_arm(bars_s + 8 * (4 + ((i - 1) & 3)), early_full);
-        pre = early_part(i - 1);
+        mbar_wait_cluster(bars_s + 8 * (4 + PH1), pe);
+        if (tid == 0 && (!GD || i - 1 >= 4)) mbar_arm(bars_s + 8 * (4 + PH1), early_full);
+        pre = early_part(PH1);
       }
+      AR_TRACE(5, pre);
     };
 
-    int i = i_top;  // 2 n_ext - 1: odd
-    for (; i >= 7; i -= 2) {
-      step(std::false_type{}, i, far_s[1], bz_s[1]);
-      step(std::false_type{}, i - 1, far_s[0], bz_s[0]);
-    }
-    for (; i >= 1; i -= 2) {
-      step(std::true_type{}, i, far_s[1], bz_s[1]);
-      step(std::true_type{}, i - 1, far_s[0], bz_s[0]);
+    // i is odd throughout (i_top = 2 n_ext - 1).  Steady state: four steps per trip, phases 3, 2, 1, 0, all four >= 5 (no
+    // "does that step exist" test).  Two guarded steps with run-time phases bring i to 3 (mod 4) when i_top = 1 (mod 4),
+    // and finish the chain (i = 7 ... 0) after the steady state; one copy of that code serves both.
+    int i = i_top;
+    while (true) {
+      if ((i & 3) == 3)
+        for (; i >= 8; i -= 4) {
+          step(std::false_type{}, PhaseConst<3>{}, i, far_s[1], bz_s[1]);
+          step(std::false_type{}, PhaseConst<2>{}, i - 1, far_s[0], bz_s[0]);
+          step(std::false_type{}, PhaseConst<1>{}, i - 2, far_s[1], bz_s[1]);
+          step(std::false_type{}, PhaseConst<0>{}, i - 3, far_s[0], bz_s[0]);
+        }
+      if (i < 1) break;
+      step(std::true_type{}, i & 3, i, far_s[1], bz_s[1]);
+      step(std::true_type{}, (i - 1) & 3, i - 1, far_s[0], bz_s[0]);
+      i -= 2;
     }
   }
   // no CTA may leave while values are still on their way to it
   cluster_barrier();
 }
 
-template <int L, int MP>
+template <int L, int MP, int NT>
 static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
-                           int n_cs, int n_sample, int n_near, int cl, cudaStream_t stream) {
-  const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16;
-  auto kernel = ar_chain_v4_kernel<L, MP>;
-  if constexpr (L == 8 && MP >= 32) {
-    // the long chains (n_cs ~ 100-160): the split between the LATE and EARLY registers as a compile-time constant.
-    // n_cs bounds the number of offset-1 samples from above, so registers [0, 4 mc) always hold all of them.
+                           int n_cs, int n_sample, int n_near, int cl, const matm_handle::ArStencil& sten,
+                           cudaStream_t stream) {
+  const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16 +
+                      ((size_t)sten.n_ring + 1) * sizeof(int) + 16 + (size_t)sten.ring_doubles * sizeof(double);
+  auto kernel = ar_chain_v4_kernel<L, MP, -1, 0, NT>;
+  if constexpr (L == 8 && NT == 256) {
+    // the production shape of every process wider than one CTA: 32 rows per CTA, so the cluster size equals
+    // mc = ceil(n_cs / 32), and n_cs bounds the number of offset-1 samples from above: registers [0, 4 mc) always hold all
+    // of them.  The LATE / EARLY split and the cluster size are compile-time constants of these instantiations.
     const int mc = (n_cs + 4 * L - 1) / (4 * L);
-    if (mc == 3) kernel = ar_chain_v4_kernel<L, MP, 3>;
-    if (mc == 4) kernel = cl == 2 ? ar_chain_v4_kernel<L, MP, 4, 2> : ar_chain_v4_kernel<L, MP, 4>;
-    if (mc == 5) kernel = cl == 3 ? ar_chain_v4_kernel<L, MP, 5, 3> : ar_chain_v4_kernel<L, MP, 5>;
+    if (mc == cl && 4 * mc <= MP) {
+      if (mc == 2) kernel = ar_chain_v4_kernel<L, MP, 2, 2, NT>;
+      if (mc == 3) kernel = ar_chain_v4_kernel<L, MP, 3, 3, NT>;
+      if (mc == 4) kernel = ar_chain_v4_kernel<L, MP, 4, 4, NT>;
+      if (mc == 5) kernel = ar_chain_v4_kernel<L, MP, 5, 5, NT>;
+    }
   }
   MATM_CUDA(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cl, 1, 1);
-  cfg.blockDim = dim3(AR_THREADS, 1, 1);
+  cfg.blockDim = dim3(NT, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -504,30 +641,91 @@ static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, cons
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, kernel, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl));
+  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, kernel, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl, sten.n_ring, sten.fence_mask));
   h->launches++;
   return MATM_OK;
 }
 
-// picks (lanes per row, samples per lane, cluster size) for the register-resident kernel; false if it does not fit
-static bool plan_v4(int n_cs, int n_sample, int* L, int* MP, int* cl) {
+// Which far samples the register-resident kernel serves from delay lines in shared memory (see the kernel): the leading ones,
+// in stencil order (offsets grow), as long as their column has an offset-1 sample and the lines fit AR_RING_DOUBLES.  What is
+// left takes the global path, which needs its smallest offset to be >= AR_GLOBAL_MIN_OFFSET; otherwise the general kernel
+// (cluster barrier per step) runs the process.  The stencil is read back from the device once and cached in the handle.
+#define AR_RING_DOUBLES 8192
+#define AR_GLOBAL_MIN_OFFSET 70  // fence every 64 steps + 4 steps of look-ahead + 2
+static int ar_stencil_info(matm_handle* h, const int32_t* esi_dev, const int32_t* csi_dev, int n_cs, int n_sample, int n_near,
+                           matm_handle::ArStencil* out) {
+  const auto key = std::make_pair((const void*)esi_dev, ((int64_t)n_sample << 32) | (uint32_t)n_near);
+  auto it = h->ar_stencil.find(key);
+  if (it != h->ar_stencil.end()) {
+    *out = it->second;
+    return MATM_OK;
+  }
+  std::vector<int32_t> esi((size_t)n_sample), csi((size_t)n_sample);
+  MATM_CUDA(h, cudaMemcpy(esi.data(), esi_dev, (size_t)n_sample * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  MATM_CUDA(h, cudaMemcpy(csi.data(), csi_dev, (size_t)n_sample * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  std::vector<char> has1((size_t)n_cs, 0);
+  bool sane = true;
+  for (int s = 0; s < n_sample; s++) {
+    if (csi[s] < 0 || csi[s] >= n_cs || esi[s] < 0) sane = false;
+    else if (s < n_near && esi[s] == 0) has1[(size_t)csi[s]] = 1;
+  }
+  matm_handle::ArStencil st = {0, 0, -1, sane ? 1 : 0};
+  if (sane) {
+    int f = n_near;
+    for (; f < n_sample; f++) {
+      const int lr = esi[f] + 1 - 3;
+      if (lr < 1 || !has1[(size_t)csi[f]] || st.ring_doubles + lr > AR_RING_DOUBLES) break;
+      if (f > n_near && esi[f] < esi[f - 1]) break;
+      st.ring_doubles += lr;
+    }
+    st.n_ring = f - n_near;
+    if (f < n_sample) {
+      int dmin = INT32_MAX;
+      for (int g = f; g < n_sample; g++) dmin = min(dmin, esi[g] + 1);
+      st.fence_mask = 63;
+      if (dmin < AR_GLOBAL_MIN_OFFSET) st.ok = 0;
+    }
+  }
+  h->ar_stencil[key] = st;
+  *out = st;
+  return MATM_OK;
+}
+
+// Picks (lanes per row, samples per lane, cluster size, threads per CTA) for the register-resident kernel; false if the
+// process does not fit it.  A step of the chain is bound by what the warps of one SM do between two barrier phases, so the
+// rows are spread thin: 256 threads per CTA (two warps per scheduler, 255 registers per thread) and at least 8 lanes per row
+// once the process is wider than one warp's worth of rows -- measured on the longest C4 layer (138 x 314, 37 368 steps):
+// 512 threads, L = 8, 3 CTAs 0.92 us/step; 512, L = 16, 5 CTAs 0.68; 256, L = 8, 5 CTAs 0.60 (profiles/r02q_chain_latency.txt).
+// 512 threads remain for the shapes whose rows would not fit 8 CTAs of 256.
+static bool plan_v4(int n_cs, int n_sample, int n_far, int* L, int* MP, int* cl, int* nt) {
   static const int Ls[4] = {4, 8, 16, 32};
-  static const int MPs[4] = {16, 24, 32, 40};
-  for (int li = 0; li < 4; li++) {
-    if (n_sample > Ls[li] * 40) continue;
-    int mp = 0;
-    for (int mi = 0; mi < 4; mi++)
-      if (n_sample <= Ls[li] * MPs[mi]) {
-        mp = MPs[mi];
-        break;
-      }
-    const int rows_per_cta = (AR_THREADS / 32) * (32 / Ls[li]);
-    const int c = (n_cs + rows_per_cta - 1) / rows_per_cta;
-    if (c > 8) continue;  // a larger L only lowers rows_per_cta further
-    *L = Ls[li];
-    *MP = mp;
-    *cl = c;
-    return true;
+  static const int MPs[5] = {16, 24, 32, 40, 48};
+  static const int NTs[2] = {256, AR_THREADS};
+  for (int ti = 0; ti < 2; ti++) {
+    const int threads = NTs[ti];
+    if (n_far > 2 * threads) continue;
+    for (int li = 0; li < 4; li++) {
+      // 48 samples per lane (96 registers of A) only where the registers are: L = 8 with 256 threads.  It keeps the six-hour
+      // layers of C5 (n_sample = 323, 327) on the 8-lane shape instead of 16 lanes x 512 threads (0.60 vs 1.35 us/step).
+      const int max_mp = (Ls[li] == 8 && threads == 256) ? 48 : 40;
+      if ((n_cs > 32 && Ls[li] < 8) || n_sample > Ls[li] * max_mp) continue;
+      if (threads == AR_THREADS && Ls[li] < 16) continue;  // instantiated for the wide stencils only
+      int mp = 0;
+      for (int mi = 0; mi < 5; mi++)
+        if (MPs[mi] <= max_mp && n_sample <= Ls[li] * MPs[mi]) {
+          mp = MPs[mi];
+          break;
+        }
+      if (Ls[li] >= 16 && mp < 24) mp = 24;
+      const int rows_per_cta = (threads / 32) * (32 / Ls[li]);
+      const int c = (n_cs + rows_per_cta - 1) / rows_per_cta;
+      if (c > 8) continue;  // a larger L only lowers rows_per_cta further
+      *L = Ls[li];
+      *MP = mp;
+      *cl = c;
+      *nt = threads;
+      return true;
+    }
   }
   return false;
 }
@@ -549,14 +747,22 @@ extern "C" int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sampl
 
   // register-resident kernel when the process fits it
   {
-    int L, mp, cl3;
-    if (n_near >= 0 && n_near <= n_sample && n_ext >= 4 && (n_sample - n_near) <= 2 * AR_THREADS &&
-        plan_v4(n_cs, n_sample, &L, &mp, &cl3)) {
-#define V4_CASE(LV, MV) \
-  if (L == LV && mp == MV) \
-    return launch_chain_v4<LV, MV>(h, A_dev, esi_dev, csi_dev, buffer_dev, n_ext, n_cs, n_sample, n_near, cl3, st);
-      V4_CASE(4, 16) V4_CASE(4, 24) V4_CASE(4, 32) V4_CASE(4, 40) V4_CASE(8, 16) V4_CASE(8, 24) V4_CASE(8, 32)
-      V4_CASE(8, 40) V4_CASE(16, 24) V4_CASE(16, 32) V4_CASE(16, 40) V4_CASE(32, 24) V4_CASE(32, 32) V4_CASE(32, 40)
+    int L, mp, cl3, nt;
+    matm_handle::ArStencil sten = {0, 0, -1, 0};
+    if (n_near >= 0 && n_near <= n_sample && n_ext >= 4 && plan_v4(n_cs, n_sample, n_sample - n_near, &L, &mp, &cl3, &nt)) {
+      int rc = ar_stencil_info(h, esi_dev, csi_dev, n_cs, n_sample, n_near, &sten);
+      if (rc) return rc;
+    }
+    if (sten.ok) {
+#define V4_CASE(LV, MV, NV) \
+  if (L == LV && mp == MV && nt == NV) \
+    return launch_chain_v4<LV, MV, NV>(h, A_dev, esi_dev, csi_dev, buffer_dev, n_ext, n_cs, n_sample, n_near, cl3, sten, st);
+      V4_CASE(4, 16, 256) V4_CASE(4, 24, 256) V4_CASE(4, 32, 256) V4_CASE(4, 40, 256)
+      V4_CASE(8, 16, 256) V4_CASE(8, 24, 256) V4_CASE(8, 32, 256) V4_CASE(8, 40, 256) V4_CASE(8, 48, 256)
+      V4_CASE(16, 24, 256) V4_CASE(16, 32, 256) V4_CASE(16, 40, 256)
+      V4_CASE(32, 24, 256) V4_CASE(32, 32, 256) V4_CASE(32, 40, 256)
+      V4_CASE(16, 24, 512) V4_CASE(16, 32, 512) V4_CASE(16, 40, 512)
+      V4_CASE(32, 24, 512) V4_CASE(32, 32, 512) V4_CASE(32, 40, 512)
 #undef V4_CASE
     }
   }

@@ -121,6 +121,12 @@ struct matm_handle {
     uint8_t* tile_m;  // (n_tiles) 1, 2 or 4: the 32 detectors of the tile come in aligned groups of that many co-located ones
   };
   std::map<std::pair<int64_t, int64_t>, DetOrder> det_order;
+  // per stencil (device pointer of esi, n_sample, n_near): how many far samples the chain kernel serves from delay lines in
+  // shared memory, their total length, and whether the rest may take the global path (matm_ar.cu)
+  struct ArStencil {
+    int n_ring, ring_doubles, fence_mask, ok;
+  };
+  std::map<std::pair<const void*, int64_t>, ArStencil> ar_stencil;
   int* flags = nullptr;
   std::vector<double> az_atm_host, el_atm_host;
   int64_t min_samples_per_interval = 0;  // over the interior spline intervals (decides the 4-samples-per-thread path)
