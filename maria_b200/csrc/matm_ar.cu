@@ -333,11 +333,25 @@ __global__ void __launch_bounds__(NT, 1)
   // lane `sub` holds the sample PAIRS 2 (sub + L q), 2 (sub + L q) + 1 in registers 2 q, 2 q + 1: one 16-byte shared-memory
   // load feeds two FMAs, and the L lanes of a row read 16 L contiguous bytes (a full 128-byte wavefront at L = 8)
   static_assert(MP % 4 == 0, "registers are consumed in groups of four (two 16-byte loads)");
+  // BLK (L = 8): register blocking.  The warp's RPW = 4 rows share every gather value, so a lane holds ALL four rows for its
+  // own SPL = MP / 4 samples (pairs 2 (lane + 32 q), + 1): one 16-byte load feeds eight FMAs and the warp reads the gather
+  // vector once instead of once per row -- the shared-memory pipe, not the FP64 pipe, was what the dot products waited for
+  // (profiles/r02t_chain_step_phases.txt).  The four partial rows are then reduced over the 32 lanes by a reduce-scatter
+  // (two exchanges that halve the rows a lane carries) followed by a three-stage butterfly, which leaves row lane / 8 in
+  // lane, i.e. the same (rr, sub) roles as the unblocked layout.
+  constexpr bool BLK = (L == 8);
+  constexpr int SPL = MP / RPW, NQ = SPL / 2;
+  static_assert(!BLK || SPL % 2 == 0, "blocked layout: whole sample pairs per lane");
   double a[MP];
 #pragma unroll
   for (int m = 0; m < MP; m++) {
-    const int s = 2 * (sub + L * (m / 2)) + (m & 1);
-    a[m] = (has_row && s < n_sample) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
+    if (BLK) {
+      const int k = m / SPL, j = m % SPL, s = 2 * (lane + 32 * (j / 2)) + (j & 1), rk = warp * RPW + k;
+      a[m] = (rk < rows && s < n_sample) ? A[(size_t)(row0 + rk) * n_sample + s] : 0.0;
+    } else {
+      const int s = 2 * (sub + L * (m / 2)) + (m & 1);
+      a[m] = (has_row && s < n_sample) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
+    }
   }
   for (int e = tid; e < 4 * gs; e += NT) G[e] = 0.0;
   for (int e = tid; e < 3 * n_cs; e += NT) pos[e] = -1;
@@ -473,25 +487,49 @@ __global__ void __launch_bounds__(NT, 1)
   cluster_barrier();
 
   // the EARLY part of the dot product of step j: registers [mcrit, MP)
-  auto early_part = [&](const int ph) -> double {  // ph = (step & 3): the gather vector of that step
-    const double2* g = reinterpret_cast<const double2*>(G + ph * gs) + sub;
-    double e0 = 0.0, e1 = 0.0, e2 = 0.0, e3 = 0.0;
+  // BLK: the LATE part is the first lq loads of a lane (64 samples each); every offset-1 sample must be inside
+  constexpr int LQC = MC >= 0 ? (MC + 1) / 2 : -1;
+  const int lq = LQC >= 0 ? LQC : min(NQ, (n1 + 63) / 64);
+  auto early_part = [&](const int ph, double(&out)[RPW]) {  // ph = (step & 3): the gather vector of that step
+    if (BLK) {
+      const double2* g = reinterpret_cast<const double2*>(G + ph * gs) + lane;
+      double ex[RPW], ey[RPW];
 #pragma unroll
-    for (int m = 0; m < MP; m += 4)
-      if (MC >= 0 ? (m >= 4 * MC) : (m >= mcrit)) {
-        const double2 v0 = g[L * (m / 2)], v1 = g[L * (m / 2 + 1)];
-        e0 = fma(a[m], v0.x, e0);
-        e1 = fma(a[m + 1], v0.y, e1);
-        e2 = fma(a[m + 2], v1.x, e2);
-        e3 = fma(a[m + 3], v1.y, e3);
-      }
-    return (e0 + e1) + (e2 + e3);
+      for (int k = 0; k < RPW; k++) ex[k] = ey[k] = 0.0;
+#pragma unroll
+      for (int q = 0; q < NQ; q++)
+        if (LQC >= 0 ? (q >= LQC) : (q >= lq)) {
+          const double2 v = g[32 * q];
+#pragma unroll
+          for (int k = 0; k < RPW; k++) {
+            ex[k] = fma(a[k * SPL + 2 * q], v.x, ex[k]);
+            ey[k] = fma(a[k * SPL + 2 * q + 1], v.y, ey[k]);
+          }
+        }
+#pragma unroll
+      for (int k = 0; k < RPW; k++) out[k] = ex[k] + ey[k];
+    } else {
+      const double2* g = reinterpret_cast<const double2*>(G + ph * gs) + sub;
+      double e0 = 0.0, e1 = 0.0, e2 = 0.0, e3 = 0.0;
+#pragma unroll
+      for (int m = 0; m < MP; m += 4)
+        if (MC >= 0 ? (m >= 4 * MC) : (m >= mcrit)) {
+          const double2 v0 = g[L * (m / 2)], v1 = g[L * (m / 2 + 1)];
+          e0 = fma(a[m], v0.x, e0);
+          e1 = fma(a[m + 1], v0.y, e1);
+          e2 = fma(a[m + 2], v1.x, e2);
+          e3 = fma(a[m + 3], v1.y, e3);
+        }
+      out[0] = (e0 + e1) + (e2 + e3);
+    }
   };
   // warps with neither a row nor a far sample only wait for the end
   const bool active = (warp * RPW < rows) || (warp * 32 < n_far);
-  double pre = 0.0;
+  double pre[RPW];
+#pragma unroll
+  for (int k = 0; k < RPW; k++) pre[k] = 0.0;
   if (active) {
-    pre = early_part(i_top & 3);
+    early_part(i_top & 3, pre);
     // this CTA's own window of the cluster's shared address space (the far samples and their barrier stay at home)
     const uint32_t bars_self = mapa_u32(bars_s, cta);
     const uint32_t far_self = mapa_u32(G_s, cta) + 8u * (n_near + tid);
@@ -511,26 +549,56 @@ __global__ void __launch_bounds__(NT, 1)
       const int ncl = CL > 0 ? CL : cl;
       const uint32_t par = ((i_top - i) >> 2) & 1;
       // (1) the row just produced has landed in G[i]
-      AR_TRACE(0, pre);
+      AR_TRACE(0, pre[0]);
       mbar_wait_cluster(bars_s + 8 * PH, par);
-      AR_TRACE(1, pre);
+      AR_TRACE(1, pre[0]);
       if (tid == 0 && (!GD || i >= 4)) mbar_arm(bars_s + 8 * PH, late_full);
       // (2) the LATE part of the dot product
-      const double2* g = reinterpret_cast<const double2*>(G + PH * gs) + sub;
-      double acc0 = pre, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+      double acc;
+      if (BLK) {
+        const double2* g = reinterpret_cast<const double2*>(G + PH * gs) + lane;
+        double ax[RPW], ay[RPW];
 #pragma unroll
-      for (int m = 0; m < MP; m += 4)
-        if (MC >= 0 ? (m < 4 * MC) : (m < mcrit)) {
-          const double2 v0 = g[L * (m / 2)], v1 = g[L * (m / 2 + 1)];
-          acc0 = fma(a[m], v0.x, acc0);
-          acc1 = fma(a[m + 1], v0.y, acc1);
-          acc2 = fma(a[m + 2], v1.x, acc2);
-          acc3 = fma(a[m + 3], v1.y, acc3);
-        }
-      double acc = (acc0 + acc1) + (acc2 + acc3);
-      AR_TRACE(2, acc);
+        for (int k = 0; k < RPW; k++) ax[k] = pre[k], ay[k] = 0.0;
 #pragma unroll
-      for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        for (int q = 0; q < NQ; q++)
+          if (LQC >= 0 ? (q < LQC) : (q < lq)) {
+            const double2 v = g[32 * q];
+#pragma unroll
+            for (int k = 0; k < RPW; k++) {
+              ax[k] = fma(a[k * SPL + 2 * q], v.x, ax[k]);
+              ay[k] = fma(a[k * SPL + 2 * q + 1], v.y, ay[k]);
+            }
+          }
+#pragma unroll
+        for (int k = 0; k < RPW; k++) ax[k] += ay[k];
+        AR_TRACE(2, ax[0]);
+        // reduce-scatter over lane bits 4 and 3 (rows 0, 1 stay in the lower half-warp, then one row per quarter), butterfly
+        // over bits 2..0: lane ends up with the full sum of row lane / 8
+        const bool hi = (lane & 16) != 0, h8 = (lane & 8) != 0;
+        const double k0 = (hi ? ax[2] : ax[0]) + __shfl_xor_sync(0xffffffffu, hi ? ax[0] : ax[2], 16);
+        const double k1 = (hi ? ax[3] : ax[1]) + __shfl_xor_sync(0xffffffffu, hi ? ax[1] : ax[3], 16);
+        acc = (h8 ? k1 : k0) + __shfl_xor_sync(0xffffffffu, h8 ? k0 : k1, 8);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+      } else {
+        const double2* g = reinterpret_cast<const double2*>(G + PH * gs) + sub;
+        double acc0 = pre[0], acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+#pragma unroll
+        for (int m = 0; m < MP; m += 4)
+          if (MC >= 0 ? (m < 4 * MC) : (m < mcrit)) {
+            const double2 v0 = g[L * (m / 2)], v1 = g[L * (m / 2 + 1)];
+            acc0 = fma(a[m], v0.x, acc0);
+            acc1 = fma(a[m + 1], v0.y, acc1);
+            acc2 = fma(a[m + 2], v1.x, acc2);
+            acc3 = fma(a[m + 3], v1.y, acc3);
+          }
+        acc = (acc0 + acc1) + (acc2 + acc3);
+        AR_TRACE(2, acc);
+#pragma unroll
+        for (int o = L / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      }
       AR_TRACE(3, acc);
       // (3) publish row r of step i into the gather vectors of steps i-1, i-2, i-3 of every CTA, and to global memory
       if (SPREAD) {
@@ -582,9 +650,9 @@ __global__ void __launch_bounds__(NT, 1)
         const uint32_t pe = ((i_top - (i - 1)) >> 2) & 1;
         mbar_wait_cluster(bars_s + 8 * (4 + PH1), pe);
         if (tid == 0 && (!GD || i - 1 >= 4)) mbar_arm(bars_s + 8 * (4 + PH1), early_full);
-        pre = early_part(PH1);
+        early_part(PH1, pre);
       }
-      AR_TRACE(5, pre);
+      AR_TRACE(5, pre[0]);
     };
 
     // i is odd throughout (i_top = 2 n_ext - 1).  Steady state: four steps per trip, phases 3, 2, 1, 0, all four >= 5 (no

@@ -42,6 +42,8 @@ def main():
         torch.cuda.synchronize()
         tr = np.zeros((16, 128, 6), dtype=np.int64)
         assert fn(tr.ctypes.data) == 0
+        n_cta = -(-n_cs // 32) if n_cs > 32 else 1
+        tr[2 * n_cta:] = 0  # slots of larger clusters traced earlier
         print(f"process {k}: n_cs {n_cs} n_sample {p.n_sample}")
         names = ["wait LATE", "LATE dot", "butterfly", "send", "EARLY+rest"]
         for slot in range(16):

@@ -313,3 +313,34 @@ def test_philox_tod_power_spectrum_matches_oracle_realisations(cuda):
     # ratio of the means within ~40 % per bin
     err = np.sqrt((dev.std(axis=0) / dev.mean(axis=0)) ** 2 + (ref.std(axis=0) / ref.mean(axis=0)) ** 2) / np.sqrt(n_real)
     assert np.all(np.abs(np.log(ratio)) < np.maximum(5 * err, 0.4)), (ratio, err)
+
+
+def test_layers_do_not_depend_on_what_else_loads_the_memory_system(cuda):
+    """The AR chain hands values between the CTAs of a cluster every half microsecond.  Whatever a CTA reads back from global
+    memory must be ordered after the store that produced it, however slow the memory system is: the same seed must give the
+    same layers bit for bit on an idle GPU and underneath a copy that saturates HBM (regression: far samples read one step
+    after they were produced came back stale under load)."""
+    cfg = configs.c4_atlast(n_det=256, duration=900.0, sample_rate=50.0)
+    sim = _device(cfg, np.float32, 37, noise="philox", seed=21, geometry="fast", pipeline_depth=1)
+    atm = sim.obs_list[0].atmosphere
+
+    def layers():
+        atm.realisation = 0  # the same Philox subsequence every time
+        atm.generate()
+        cuda.cuda.synchronize()
+        return [p.values_device.clone() for p in atm.processes.values()]
+
+    quiet = layers()
+    assert all(bool(cuda.isfinite(v).all()) for v in quiet)
+    src = cuda.empty(1 << 28, dtype=cuda.float32, device=atm.ctx.device).normal_()  # 1 GiB
+    dst = cuda.empty_like(src)
+    side = cuda.cuda.Stream(device=atm.ctx.device)
+    for trial in range(3):
+        side.wait_stream(cuda.cuda.current_stream(atm.ctx.device))
+        with cuda.cuda.stream(side):
+            for _ in range(60):  # ~20 ms of HBM-bound traffic: longer than the chains
+                dst.copy_(src)
+        loaded = layers()
+        side.synchronize()
+        for k, (a, b) in enumerate(zip(quiet, loaded)):
+            assert cuda.equal(a, b), (trial, k)
