@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(NT, 1)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int gs = L * MP;                                     // padded length of one gather vector
   double* G = reinterpret_cast<double*>(smem_raw);           // [4][gs]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(G + 4 * (size_t)gs);  // [4] LATE, [4] EARLY
+  uint64_t* bars = reinterpret_cast<uint64_t*>(G + 4 * (size_t)gs);  // [4]: one transaction barrier per gather vector (slots 4..7 unused)
   int* cnt = reinterpret_cast<int*>(bars + 8);               // [4]: near samples of offset 1, 2, 3
   int* pos = cnt + 4;                                        // [3][n_cs]: position of column c among the samples of offset 1, 2, 3
   const int n_far = n_sample - n_near;
@@ -357,7 +357,7 @@ __global__ void __launch_bounds__(NT, 1)
   for (int e = tid; e < 3 * n_cs; e += NT) pos[e] = -1;
   if (tid < 4) cnt[tid] = 0;
   if (tid == 0) {
-    for (int b = 0; b < 8; b++) mbar_init(bars + b, 1);
+    for (int b = 0; b < 4; b++) mbar_init(bars + b, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(NT, 1)
       const int pk = (has_row && t < 3 * cl) ? pos[(k - 1) * n_cs + row0 + r] : -1;
       pubk[j] = pk >= 0 ? k : 0;
       pubd[j] = mapa_u32(G_s, c) + 8u * max(pk, 0);
-      pubb[j] = mapa_u32(bars_s, c) + (k == 1 ? 0u : 32u);
+      pubb[j] = mapa_u32(bars_s, c);
     }
   }
   // ---- prologue: the initial-noise rows i_top+1 .. i_top+3 feed steps i_top, i_top-1, i_top-2 ----
@@ -473,15 +473,18 @@ __global__ void __launch_bounds__(NT, 1)
       if (i_top >= 3) far_s[0][q] = buffer[(size_t)(i_top - 3) * n_cs + foff[q]];
     }
   // bytes each barrier expects for step j = i_top - d: what the loop (not the prologue) delivers
-  const uint32_t late_full = 8u * n1, early_full = 8u * (n2 + n3 + n_far);
+  // ONE transaction barrier per step: everything sent during step j + 1 -- row j + 1 at its offsets 1, 2, 3 (vectors of
+  // steps j, j - 1, j - 2) and the far samples of the vector of step j - 1 -- completes bytes on the barrier step j waits for.
+  // Passing it therefore also proves the EARLY entries of the vector of step j - 1 complete (offset 2: this row; offset 3 and
+  // far: a barrier passed one step earlier), so the EARLY part needs no wait of its own.
+  auto step_bytes = [&](const int j) -> uint32_t {  // what the loop delivers for step j (vectors of negative steps are not sent)
+    return 8u * (n1 + (j >= 1 ? n2 + n_far : 0) + (j >= 2 ? n3 : 0));
+  };
   if (tid == 0) {
     for (int d = 0; d < 4 && d <= i_top; d++) {
       const int b = (i_top - d) & 3;
-      mbar_arm(bars_s + 8 * b, d >= 1 ? late_full : 0u);
-      mbar_arm(bars_s + 8 * (4 + b), (d >= 2 ? 8u * (n2 + n_far) : 0u) + (d >= 3 ? 8u * n3 : 0u));
+      mbar_arm(bars_s + 8 * b, d >= 1 ? step_bytes(i_top - d) : 0u);  // row i_top + 1 is initial noise: placed by the prologue
     }
-    // nobody waits for the EARLY barrier of step i_top (its part is computed right below): arm its next use here
-    if (i_top >= 4) mbar_arm(bars_s + 8 * (4 + (i_top & 3)), early_full);
   }
   __syncthreads();
   cluster_barrier();
@@ -552,7 +555,7 @@ __global__ void __launch_bounds__(NT, 1)
       AR_TRACE(0, pre[0]);
       mbar_wait_cluster(bars_s + 8 * PH, par);
       AR_TRACE(1, pre[0]);
-      if (tid == 0 && (!GD || i >= 4)) mbar_arm(bars_s + 8 * PH, late_full);
+      if (tid == 0 && (!GD || i >= 4)) mbar_arm(bars_s + 8 * PH, GD ? step_bytes(i - 4) : 8u * n_sample);
       // (2) the LATE part of the dot product
       double acc;
       if (BLK) {
@@ -607,14 +610,14 @@ __global__ void __launch_bounds__(NT, 1)
 #pragma unroll
         for (int j = 0; j < NJ; j++) {
           const int bsel = (PH - pubk[j]) & 3;
-          st_async_f64_if(pubk[j] != 0 && (!GD || i >= pubk[j]), pubd[j] + 8u * (bsel * gs), v, pubb[j] + 8u * bsel);
+          st_async_f64_if(pubk[j] != 0 && (!GD || i >= pubk[j]), pubd[j] + 8u * (bsel * gs), v, pubb[j] + 8u * PH1);
         }
       } else
       if (has_row && sub == 0) {
         const double v = bz + acc;
         const uint32_t d1 = G_s + 8u * (PH1 * gs + p1), b1 = bars_s + 8u * PH1;
-        const uint32_t d2 = G_s + 8u * (PH2 * gs + p2), b2 = bars_s + 8u * (4 + PH2);
-        const uint32_t d3 = G_s + 8u * (PH3 * gs + p3), b3 = bars_s + 8u * (4 + PH3);
+        const uint32_t d2 = G_s + 8u * (PH2 * gs + p2), b2 = b1;
+        const uint32_t d3 = G_s + 8u * (PH3 * gs + p3), b3 = b1;
         buffer[(uint32_t)(i * n_cs + myrow)] = v;  // read again (far samples) no sooner than three steps from now
 #pragma unroll
         for (int c = 0; c < (CL > 0 ? CL : 8); c++) {
@@ -628,7 +631,7 @@ __global__ void __launch_bounds__(NT, 1)
       // (4) off the critical path: send the far values of step i - 2 (in flight since step i + 4), re-issue the set for
       //     step i - 4 (rows >= i + 1, complete: their LATE barrier was passed above), re-issue B z for step i - 2
       {
-        const uint32_t be = bars_self + 8u * (4 + PH2);
+        const uint32_t be = bars_self + 8u * PH1;
 #pragma unroll
         for (int q = 0; q < 2; q++)
           if (foff[q] >= 0) {
@@ -647,9 +650,6 @@ __global__ void __launch_bounds__(NT, 1)
       if ((!GD || i >= 2) && has_row) bz = __ldcg(buffer + (uint32_t)((i - 2) * n_cs + myrow));
       // (5) the EARLY part of step i - 1, while the row of step i is on its way
       if (!GD || i >= 1) {
-        const uint32_t pe = ((i_top - (i - 1)) >> 2) & 1;
-        mbar_wait_cluster(bars_s + 8 * (4 + PH1), pe);
-        if (tid == 0 && (!GD || i - 1 >= 4)) mbar_arm(bars_s + 8 * (4 + PH1), early_full);
         early_part(PH1, pre);
       }
       AR_TRACE(5, pre[0]);
