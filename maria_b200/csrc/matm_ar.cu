@@ -303,6 +303,11 @@ __device__ __forceinline__ constexpr int phase_value(int v) { return v; }
 // MC >= 0: the LATE part is registers [0, 4 MC), fixed at compile time; CL > 0: the cluster size, fixed at compile time
 // NT: threads per CTA.  512 = 128 registers per thread and up to 16 warps of rows per SM (the smallest cluster); 256 = 255
 // registers, 8 warps (two per scheduler): fewer rows per SM, more CTAs per cluster, a shorter step.
+// The LAST warp of the CTA owns the far samples and no rows, so that no warp on the critical path of a row carries them
+// (profiles/r02t_chain_step_phases.txt: the warps that also served far samples were the ones everybody waited for); the
+// other NT / 32 - 1 warps hold (NT / 32 - 1) * (32 / L) rows.  (A ninth warp next to eight row warps does not pay: registers
+// are allocated as if the block had a multiple of four warps, 288 threads would be budgeted as 384.)
+#define AR_FAR_Q 4  // far samples per lane of that warp: n_far <= 128
 template <int L, int MP, int MC = -1, int CL = 0, int NT = AR_THREADS>
 __global__ void __launch_bounds__(NT, 1)
     ar_chain_v4_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
@@ -323,9 +328,11 @@ __global__ void __launch_bounds__(NT, 1)
   const int row0 = cta * rpc;
   const int rows = max(0, min(n_cs, row0 + rpc) - row0);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NTT = NT;                            // all threads of the CTA (set-up loops)
+  const bool far_warp = warp == NT / 32 - 1;         // the last warp: far samples only, no rows
   const int rr = lane / L, sub = lane % L;
   const int r = warp * RPW + rr;  // row within this CTA
-  const bool has_row = r < rows;
+  const bool has_row = r < rows && !far_warp;
   const int i_top = 2 * n_ext - 1;
   const uint32_t G_s = smem_u32(G), bars_s = smem_u32(bars);
 
@@ -353,23 +360,23 @@ __global__ void __launch_bounds__(NT, 1)
       a[m] = (has_row && s < n_sample) ? A[(size_t)(row0 + r) * n_sample + s] : 0.0;
     }
   }
-  for (int e = tid; e < 4 * gs; e += NT) G[e] = 0.0;
-  for (int e = tid; e < 3 * n_cs; e += NT) pos[e] = -1;
+  for (int e = tid; e < 4 * gs; e += NTT) G[e] = 0.0;
+  for (int e = tid; e < 3 * n_cs; e += NTT) pos[e] = -1;
   if (tid < 4) cnt[tid] = 0;
   if (tid == 0) {
     for (int b = 0; b < 4; b++) mbar_init(bars + b, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  for (int s = tid; s < n_near; s += NT) {
+  for (int s = tid; s < n_near; s += NTT) {
     pos[esi[s] * n_cs + csi[s]] = s;  // offset = esi + 1 in 1..3
     atomicAdd(&cnt[esi[s]], 1);
   }
-  int foff[2];
+  int foff[AR_FAR_Q];  // far sample lane + 32 q of the far warp: element offset of (row + d, column) relative to the row
 #pragma unroll
-  for (int q = 0; q < 2; q++) {
-    const int f = tid + q * NT;
-    foff[q] = f < n_far ? (esi[n_near + f] + 1) * n_cs + csi[n_near + f] : -1;
+  for (int q = 0; q < AR_FAR_Q; q++) {
+    const int f = lane + 32 * q;
+    foff[q] = (far_warp && f < n_far) ? (esi[n_near + f] + 1) * n_cs + csi[n_near + f] : -1;
   }
   __syncthreads();
   const int n1 = cnt[0], n2 = cnt[1], n3 = cnt[2];
@@ -395,17 +402,17 @@ __global__ void __launch_bounds__(NT, 1)
   __syncthreads();
   for (int f = 0; f < n_ring; f++) {
     const int lr = esi[n_near + f] + 1 - 3, c = csi[n_near + f], ro = roff[f];
-    for (int k = tid; k < lr; k += NT) {  // rows i_top + 2 ... i_top - 2 + d: the initial noise, written by an earlier kernel
+    for (int k = tid; k < lr; k += NTT) {  // rows i_top + 2 ... i_top - 2 + d: the initial noise, written by an earlier kernel
       const int row = i_top + 2 + k;
       ring[ro + row % lr] = buffer[(size_t)row * n_cs + c];
     }
   }
-  uint32_t ring_p[2], ring_lo[2], ring_hi[2], ring_src[2];
+  uint32_t ring_p[AR_FAR_Q], ring_lo[AR_FAR_Q], ring_hi[AR_FAR_Q], ring_src[AR_FAR_Q];
 #pragma unroll
-  for (int q = 0; q < 2; q++) {
-    const int f = tid + q * NT;
+  for (int q = 0; q < AR_FAR_Q; q++) {
+    const int f = lane + 32 * q;
     ring_p[q] = ring_lo[q] = ring_hi[q] = ring_src[q] = 0u;
-    if (f < n_ring) {
+    if (far_warp && f < n_ring) {
       const int d = esi[n_near + f] + 1, lr = d - 3;
       ring_lo[q] = smem_u32(ring + roff[f]);
       ring_hi[q] = ring_lo[q] + 8u * (lr - 1);
@@ -443,31 +450,32 @@ __global__ void __launch_bounds__(NT, 1)
     }
   }
   // ---- prologue: the initial-noise rows i_top+1 .. i_top+3 feed steps i_top, i_top-1, i_top-2 ----
-  for (int e = tid; e < 3 * n_near; e += NT) {
+  for (int e = tid; e < 3 * n_near; e += NTT) {
     const int k = e / n_near, s = e % n_near;  // step i_top - k, near sample s
     const int off = esi[s] + 1;
     if (off > k && i_top - k >= 0)
       G[((i_top - k) & 3) * gs + s] = buffer[(size_t)(i_top - k + off) * n_cs + csi[s]];
   }
 #pragma unroll
-  for (int q = 0; q < 2; q++)
+  for (int q = 0; q < AR_FAR_Q; q++)
     if (foff[q] >= 0) {
-      const int f = n_near + tid + q * NT;
+      const int f = n_near + lane + 32 * q;
       G[(i_top & 3) * gs + f] = buffer[(size_t)i_top * n_cs + foff[q]];
       if (i_top >= 1) G[((i_top - 1) & 3) * gs + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
     }
   // Register pipelines, two sets each, used alternately by even / odd steps (the loop is unrolled by two):
   //   far_s[i & 1]: issued at step i + 4 for step i - 2, sent into G at step i, then re-issued for step i - 4
   //   bz_s[i & 1] : issued at step i + 2 for step i, consumed when step i publishes, then re-issued for step i - 2
-  double far_s[2][2], bz_s[2];
-  far_s[0][0] = far_s[0][1] = far_s[1][0] = far_s[1][1] = 0.0;
+  double far_s[2][AR_FAR_Q], bz_s[2];
+#pragma unroll
+  for (int q = 0; q < AR_FAR_Q; q++) far_s[0][q] = far_s[1][q] = 0.0;
   bz_s[0] = bz_s[1] = 0.0;
   if (has_row) {  // i_top is odd: set 1 serves step i_top, set 0 step i_top - 1
     bz_s[1] = buffer[(size_t)i_top * n_cs + row0 + r];
     bz_s[0] = buffer[(size_t)(i_top - 1) * n_cs + row0 + r];
   }
 #pragma unroll
-  for (int q = 0; q < 2; q++)
+  for (int q = 0; q < AR_FAR_Q; q++)
     if (foff[q] >= 0) {
       if (i_top >= 2) far_s[1][q] = buffer[(size_t)(i_top - 2) * n_cs + foff[q]];
       if (i_top >= 3) far_s[0][q] = buffer[(size_t)(i_top - 3) * n_cs + foff[q]];
@@ -527,15 +535,13 @@ __global__ void __launch_bounds__(NT, 1)
     }
   };
   // warps with neither a row nor a far sample only wait for the end
-  const bool active = (warp * RPW < rows) || (warp * 32 < n_far);
+  const bool active = warp * RPW < rows && !far_warp;
   double pre[RPW];
 #pragma unroll
   for (int k = 0; k < RPW; k++) pre[k] = 0.0;
   if (active) {
     early_part(i_top & 3, pre);
     // this CTA's own window of the cluster's shared address space (the far samples and their barrier stay at home)
-    const uint32_t bars_self = mapa_u32(bars_s, cta);
-    const uint32_t far_self = mapa_u32(G_s, cta) + 8u * (n_near + tid);
 
     // GD = false: the steady state (i >= 5), where every "does that step exist" test below is true
     // element offsets inside BUFFER fit 31 bits (3 n_ext n_cs <= INT32_MAX is checked by the host): 32-bit index arithmetic
@@ -546,7 +552,7 @@ __global__ void __launch_bounds__(NT, 1)
 #endif
     // `phase` = i & 3, the gather vector of step i: a compile-time constant in the steady state (the loop below is unrolled
     // by four), so that every shared-memory address of the step is a register plus an immediate
-    auto step = [&](auto guard, auto phase, const int i, double(&fs)[2], double& bz) {
+    auto step = [&](auto guard, auto phase, const int i, double& bz) {
       constexpr bool GD = decltype(guard)::value;
       const int PH = phase_value(phase), PH1 = (PH + 3) & 3, PH2 = (PH + 2) & 3, PH3 = (PH + 1) & 3;  // steps i, i - 1, i - 2, i - 3
       const int ncl = CL > 0 ? CL : cl;
@@ -628,24 +634,8 @@ __global__ void __launch_bounds__(NT, 1)
         }
       }
       AR_TRACE(4, acc);
-      // (4) off the critical path: send the far values of step i - 2 (in flight since step i + 4), re-issue the set for
-      //     step i - 4 (rows >= i + 1, complete: their LATE barrier was passed above), re-issue B z for step i - 2
-      {
-        const uint32_t be = bars_self + 8u * PH1;
-#pragma unroll
-        for (int q = 0; q < 2; q++)
-          if (foff[q] >= 0) {
-            double v = fs[q];
-            if (ring_hi[q] != 0u) {  // delay line: take (i - 2 + d, c) out, put (i + 1, c) in its place
-              const double vnew = lds_f64(G_s + 8u * (PH * gs) + ring_src[q]);
-              v = lds_f64(ring_p[q]);
-              sts_f64(ring_p[q], vnew);
-              ring_p[q] = ring_p[q] == ring_lo[q] ? ring_hi[q] : ring_p[q] - 8u;
-            }
-            if (!GD || i >= 2) st_async_f64(far_self + 8u * (PH2 * gs + q * NT), v, be);
-            if (ring_hi[q] == 0u && (!GD || i >= 4)) fs[q] = __ldcg(buffer + (uint32_t)((i - 4) * n_cs + foff[q]));
-          }
-      }
+      // (4) off the critical path: the periodic fence that orders this thread's row stores for the far warp's reads of BUFFER,
+      //     and B z for step i - 2 (the far samples themselves are the far warp's business)
       if (fence_mask >= 0 && (i & fence_mask) == 0) __threadfence();
       if ((!GD || i >= 2) && has_row) bz = __ldcg(buffer + (uint32_t)((i - 2) * n_cs + myrow));
       // (5) the EARLY part of step i - 1, while the row of step i is on its way
@@ -662,15 +652,45 @@ __global__ void __launch_bounds__(NT, 1)
     while (true) {
       if ((i & 3) == 3)
         for (; i >= 8; i -= 4) {
-          step(std::false_type{}, PhaseConst<3>{}, i, far_s[1], bz_s[1]);
-          step(std::false_type{}, PhaseConst<2>{}, i - 1, far_s[0], bz_s[0]);
-          step(std::false_type{}, PhaseConst<1>{}, i - 2, far_s[1], bz_s[1]);
-          step(std::false_type{}, PhaseConst<0>{}, i - 3, far_s[0], bz_s[0]);
+          step(std::false_type{}, PhaseConst<3>{}, i, bz_s[1]);
+          step(std::false_type{}, PhaseConst<2>{}, i - 1, bz_s[0]);
+          step(std::false_type{}, PhaseConst<1>{}, i - 2, bz_s[1]);
+          step(std::false_type{}, PhaseConst<0>{}, i - 3, bz_s[0]);
         }
       if (i < 1) break;
-      step(std::true_type{}, i & 3, i, far_s[1], bz_s[1]);
-      step(std::true_type{}, (i - 1) & 3, i - 1, far_s[0], bz_s[0]);
+      step(std::true_type{}, i & 3, i, bz_s[1]);
+      step(std::true_type{}, (i - 1) & 3, i - 1, bz_s[0]);
       i -= 2;
+    }
+  }
+  if (far_warp && n_far > 0) {
+    // The far warp.  Step i: wait for the barrier of step i (row i + 1 is complete in the LATE part of this CTA's vector of
+    // step i), move every delay line on by one, send the far values of the vector of step i - 2 (bytes complete on the
+    // barrier of step i - 1, like everything else sent during step i).  Samples beyond the delay lines (offset >= 70) come
+    // from BUFFER, loaded four steps ahead into two register sets used by even / odd steps.
+    const uint32_t bars_self = mapa_u32(bars_s, cta);
+    const uint32_t far_self = mapa_u32(G_s, cta) + 8u * (n_near + lane);
+    auto far_step = [&](const int i, double(&fs)[AR_FAR_Q]) {
+      const int PH = i & 3, PH1 = (PH + 3) & 3, PH2 = (PH + 2) & 3;
+      mbar_wait_cluster(bars_s + 8 * PH, ((i_top - i) >> 2) & 1);
+      const uint32_t be = bars_self + 8u * PH1;
+#pragma unroll
+      for (int q = 0; q < AR_FAR_Q; q++)
+        if (foff[q] >= 0) {
+          double v = fs[q];
+          if (ring_hi[q] != 0u) {  // delay line: take (i - 2 + d, c) out, put (i + 1, c) in its place
+            const double vnew = lds_f64(G_s + 8u * (PH * gs) + ring_src[q]);
+            v = lds_f64(ring_p[q]);
+            sts_f64(ring_p[q], vnew);
+            ring_p[q] = ring_p[q] == ring_lo[q] ? ring_hi[q] : ring_p[q] - 8u;
+          }
+          if (i >= 2) st_async_f64(far_self + 8u * (PH2 * gs + 32 * q), v, be);
+          if (ring_hi[q] == 0u && i >= 4) fs[q] = __ldcg(buffer + (uint32_t)((i - 4) * n_cs + foff[q]));
+        }
+    };
+    for (int i = i_top; i >= 1; i -= 2) {  // i_top is odd
+      far_step(i, far_s[1]);
+      far_step(i - 1, far_s[0]);
     }
   }
   // no CTA may leave while values are still on their way to it
@@ -685,16 +705,16 @@ static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, cons
                       ((size_t)sten.n_ring + 1) * sizeof(int) + 16 + (size_t)sten.ring_doubles * sizeof(double);
   auto kernel = ar_chain_v4_kernel<L, MP, -1, 0, NT>;
   if constexpr (L == 8 && NT == 256) {
-    // the production shape of every process wider than one CTA: 32 rows per CTA, so the cluster size equals
-    // mc = ceil(n_cs / 32), and n_cs bounds the number of offset-1 samples from above: registers [0, 4 mc) always hold all
-    // of them.  The LATE / EARLY split and the cluster size are compile-time constants of these instantiations.
+    // the production shape of every process wider than one CTA: 7 row warps x 4 rows = 28 rows per CTA.  mc = ceil(n_cs / 32)
+    // bounds the LATE part (n_cs bounds the number of offset-1 samples from above: the first ceil(mc / 2) loads of a lane
+    // always hold all of them); the cluster is mc or mc + 1 CTAs.  Both are compile-time constants of these instantiations.
     const int mc = (n_cs + 4 * L - 1) / (4 * L);
-    if (mc == cl && 4 * mc <= MP) {
-      if (mc == 2) kernel = ar_chain_v4_kernel<L, MP, 2, 2, NT>;
-      if (mc == 3) kernel = ar_chain_v4_kernel<L, MP, 3, 3, NT>;
-      if (mc == 4) kernel = ar_chain_v4_kernel<L, MP, 4, 4, NT>;
-      if (mc == 5) kernel = ar_chain_v4_kernel<L, MP, 5, 5, NT>;
-    }
+#define V4_PICK(MCV, CLV) \
+  if (mc == MCV && cl == CLV) kernel = ar_chain_v4_kernel<L, MP, MCV, CLV, NT>;
+    if constexpr (MP <= 32) { V4_PICK(2, 2) V4_PICK(2, 3) }
+    if constexpr (MP >= 24 && MP <= 40) { V4_PICK(3, 3) V4_PICK(3, 4) }
+    if constexpr (MP >= 32) { V4_PICK(4, 4) V4_PICK(4, 5) V4_PICK(5, 5) V4_PICK(5, 6) }
+#undef V4_PICK
   }
   MATM_CUDA(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
@@ -771,7 +791,7 @@ static bool plan_v4(int n_cs, int n_sample, int n_far, int* L, int* MP, int* cl,
   static const int NTs[2] = {256, AR_THREADS};
   for (int ti = 0; ti < 2; ti++) {
     const int threads = NTs[ti];
-    if (n_far > 2 * threads) continue;
+    if (n_far > 32 * AR_FAR_Q) continue;
     for (int li = 0; li < 4; li++) {
       // 48 samples per lane (96 registers of A) only where the registers are: L = 8 with 256 threads.  It keeps the six-hour
       // layers of C5 (n_sample = 323, 327) on the 8-lane shape instead of 16 lanes x 512 threads (0.60 vs 1.35 us/step).
@@ -785,7 +805,7 @@ static bool plan_v4(int n_cs, int n_sample, int n_far, int* L, int* MP, int* cl,
           break;
         }
       if (Ls[li] >= 16 && mp < 24) mp = 24;
-      const int rows_per_cta = (threads / 32) * (32 / Ls[li]);
+      const int rows_per_cta = (threads / 32 - 1) * (32 / Ls[li]);  // the last warp serves the far samples
       const int c = (n_cs + rows_per_cta - 1) / rows_per_cta;
       if (c > 8) continue;  // a larger L only lowers rows_per_cta further
       *L = Ls[li];
