@@ -404,8 +404,9 @@ def strong_block(args, torch, dist, rank, world, device, steps, n1_value):
     cfg = configs.c4_atlast(n_det=per, duration=args.duration or 3600.0, sample_rate=args.sample_rate, n_groups=world)
     n, n_t = cfg["instrument"].dets.n, len(cfg["plan"].time)
     det0, cnt = rank * per, per
-    # a realisation cannot finish faster than its longest AR chain (~40 ms): enough realisations in flight to cover it
-    depth = int(min(16, max(args.depth, np.ceil(45.0 * world / 27.0) + 1)))
+    # a realisation cannot finish faster than its longest AR chain (~22 ms + noise and smoothing): enough realisations in
+    # flight to cover it behind the 1 / world share of a 22 ms synthesis
+    depth = int(min(16, max(args.depth, np.ceil(26.0 * world / 22.0) + 1)))
     sim = make_sim(cfg, (det0, cnt), device, depth, exchange=True)
     atm = sim.obs_list[0].atmosphere
     atm.set_gain(np.exp(cfg["instrument"].dets.gain_error * np.random.standard_normal(size=n)))
@@ -513,8 +514,8 @@ def run_b200(args):
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.depth is None:
-        # C5's longest layer is a ~300 ms chain (223 k dependent steps); one rank synthesises its shard in ~200 / N ms
-        args.depth = 3 if args.config != "c5" else int(min(16, max(3, np.ceil(300.0 * world / 200.0) + 2)))
+        # C5's longest layer is a ~140 ms chain (223 k dependent steps); one rank synthesises its shard in ~180 / N ms
+        args.depth = 3 if args.config != "c5" else int(min(16, max(3, np.ceil(160.0 * world / 180.0) + 2)))
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

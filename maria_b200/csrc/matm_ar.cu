@@ -4,10 +4,10 @@
 //
 // Three kernels.  (1) bz_gemm_kernel: the only genuinely dense contraction, B @ z for ALL steps at once
 // (M = 2 n_ext, N = K = n_cs), written straight into BUFFER rows [0, 2 n_ext).  (2) ar_chain_v4_kernel: the sequential
-// recurrence of every process that fits it (all "2d" processes: n_sample <= 1280, n_cs <= 8 x 128): one thread-block
-// cluster per process, A in REGISTERS (L lanes per row), the gather vectors in shared memory, every produced value sent
-// with st.async into the gather vectors of the next three steps of every CTA of the cluster, completing bytes on mbarriers
-// of the destination CTA -- no cluster barrier, no fence on the critical path.  (3) ar_chain_kernel: the general
+// recurrence of every process that fits it (all "2d" processes: n_sample <= 1280, at most 128 far samples, rows that fit 8
+// CTAs): one thread-block cluster per process, A in REGISTERS, the gather vectors in shared memory, every produced value
+// sent with st.async into the gather vectors of the next three steps of every CTA of the cluster, completing bytes on an
+// mbarrier of the destination CTA -- no cluster barrier, no fence on the critical path.  (3) ar_chain_kernel: the general
 // recurrence for larger processes (the coupled "3d" model: n_cs and n_sample in the thousands): every CTA of the cluster
 // keeps its slice of rows of A in shared memory when it fits (staged once with the TMA bulk-copy engine), else streams
 // it from L2; the gather vector is rebuilt from the L2-resident BUFFER each step and the CTAs meet at a hardware cluster
@@ -196,22 +196,25 @@ __device__ __forceinline__ void cluster_barrier() {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// The chain, v4.  A step is bounded by the round trips on its critical path, not by arithmetic, so everything that is not
-// "the previous row" is taken off that path and the rest is made short:
-//   * A lives in REGISTERS.  L lanes share a row (32 / L rows per warp): lane `sub` holds the entries of samples
-//     sub, sub + L, ...  ->  the cross-lane reduction is log2(L) shuffle stages instead of 5 per row;
+// The chain, v4.  A step is bounded by what lies between "the previous row has landed" and "this row has left", not by
+// arithmetic, so everything that is not the previous row is taken off that path and the rest is made short:
+//   * A lives in REGISTERS.  L lanes share a row (32 / L rows per warp).  At L = 8 (every process wider than 32 columns)
+//     the layout is register-blocked: a lane holds all four rows of its warp for its own samples, so the warp reads a
+//     gather vector once, with 16-byte loads, and the four partial rows are reduced by a reduce-scatter + butterfly;
 //   * the gather vector of step i is a contiguous shared-memory array G[i & 3][n_sample]: whoever produces a value
-//     writes it straight to where its consumers will read it; the stencil rows further back (offsets >= 4) plus the row's
-//     own B z term are fetched from L2 ahead of their use through a register pipeline, so their latency never shows;
-//   * no barrier: data-carrying signals.
-// Every value travels with its own completion: the owner of (row i, column c) sends it with st.async into the gather
-// vectors of steps i-1, i-2, i-3 of every CTA, each store completing bytes on an mbarrier of the DESTINATION CTA.  A
-// gather vector has two mbarriers: EARLY (stencil offsets 2, 3 and the far samples: everything known one step ahead)
-// and LATE (offset 1: the row just produced).  A step therefore waits only for the bytes it needs, there is no fence
-// and no barrier round trip on the critical path, and the part of the dot product that uses the EARLY entries of the
-// NEXT step (more than half of a row of A) is computed while the LATE entries are still in flight.
-// Buffer reuse needs no extra synchronisation: a value of step i can only be sent after the LATE barrier of step i
-// completed, i.e. after every publishing warp of every CTA has finished reading the vectors of steps > i.
+//     writes it straight to where its consumers will read it;
+//   * no cluster barrier, no fence on the critical path: data-carrying signals.  The owner of (row i, column c) sends the
+//     value with st.async into the gather vectors of steps i-1, i-2, i-3 of every CTA; every store completes bytes on ONE
+//     mbarrier of the destination CTA, the one step i-1 waits for.  The part of the dot product that uses the entries
+//     known one step ahead (offsets 2, 3 and the far samples: more than half of a row of A) is computed while the row just
+//     sent is still in flight;
+//   * the far samples (offsets >= 4) are the business of the CTA's last warp, which holds no rows: per sample a delay line
+//     in shared memory fed from the row that every CTA receives anyway (offsets < 70), BUFFER in global memory behind a
+//     periodic fence for the rest.  Nothing is ever read back from global memory sooner than 66 steps after it was stored;
+//   * 256 threads per CTA (7 row warps + the far warp: two warps per scheduler, no register cap), the step loop unrolled by
+//     four so that the phase (i & 3) of every shared-memory address is an immediate.
+// Buffer reuse needs no extra synchronisation: a value of step i can only be sent after the barrier of step i completed,
+// i.e. after every warp of every CTA has finished reading the vectors of steps > i.
 // ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t a, int cta) {
   uint32_t r;

@@ -1,5 +1,5 @@
 """Digest of an .ncu-rep: key raw metrics + instruction / stall-sample share per SASS region.
-usage: python scripts/ncu_digest.py report.ncu-rep [n_output_samples] [bucket]"""
+usage: python scripts/ncu_digest.py report.ncu-rep [n_output_samples] [bucket] [kernel index in the report]"""
 import csv
 import io
 import subprocess
@@ -8,7 +8,9 @@ import sys
 rep = sys.argv[1]
 n_out = float(sys.argv[2]) if len(sys.argv) > 2 else None
 bucket = int(sys.argv[3]) if len(sys.argv) > 3 else 100
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+kid = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+sel = ["--launch-skip", str(kid), "--launch-count", "1"] if kid else []
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", *sel], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rows[0], rows[1], rows[2]
 want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -26,11 +28,11 @@ for w in want:
         print(f"{w:70s} {vals[i]:>22s} {units[i]}")
 if n_out and "smsp__thread_inst_executed.sum" in d:
     print(f"thread instructions per output sample: {float(d['smsp__thread_inst_executed.sum'].replace(',', '')) / n_out:.1f}")
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", *sel], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
 h = rows[1]
 ia, ie, isamp = h.index("Source"), h.index("Instructions Executed"), h.index("# Samples")
-data = rows[2:]
+data = [r for r in rows[2:] if len(r) > max(ie, isamp) and r[ie].isdigit()]
 tot = sum(int(r[ie]) for r in data)
 ts = sum(int(r[isamp]) for r in data) or 1
 print(f"SASS instructions: {len(data)}, warp-instructions executed {tot}")
