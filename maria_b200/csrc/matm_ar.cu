@@ -209,8 +209,10 @@ __device__ __forceinline__ void cluster_barrier() {
 //     known one step ahead (offsets 2, 3 and the far samples: more than half of a row of A) is computed while the row just
 //     sent is still in flight;
 //   * the far samples (offsets >= 4) are the business of the CTA's last warp, which holds no rows: per sample a delay line
-//     in shared memory fed from the row that every CTA receives anyway (offsets < 70), BUFFER in global memory behind a
-//     periodic fence for the rest.  Nothing is ever read back from global memory sooner than 66 steps after it was stored;
+//     in shared memory fed from the row that every CTA receives anyway (offsets < 600), BUFFER in global memory behind a
+//     periodic fence for the rest.  Nothing is ever read back from global memory sooner than 566 steps after it was stored,
+//     and what a step needs from global memory (those samples, the row's B z term) is prefetched 32 steps ahead with
+//     cp.async by the same warp: the chain keeps its pace underneath kernels that saturate HBM;
 //   * 256 threads per CTA (7 row warps + the far warp: two warps per scheduler, no register cap), the step loop unrolled by
 //     four so that the phase (i & 3) of every shared-memory address is an immediate.
 // Buffer reuse needs no extra synchronisation: a value of step i can only be sent after the barrier of step i completed,
@@ -233,6 +235,9 @@ __device__ __forceinline__ double lds_f64(uint32_t addr) {
 }
 __device__ __forceinline__ void sts_f64(uint32_t addr, double v) {
   asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void cp_async_f64(uint32_t dst_smem, const double* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst_smem), "l"(src) : "memory");
 }
 // the same under a predicate inside the instruction stream: no branch, no reconvergence point around the store
 __device__ __forceinline__ void st_async_f64_if(bool p, uint32_t remote_addr, double v, uint32_t remote_bar) {
@@ -311,10 +316,15 @@ __device__ __forceinline__ constexpr int phase_value(int v) { return v; }
 // other NT / 32 - 1 warps hold (NT / 32 - 1) * (32 / L) rows.  (A ninth warp next to eight row warps does not pay: registers
 // are allocated as if the block had a multiple of four warps, 288 threads would be budgeted as 384.)
 #define AR_FAR_Q 4  // far samples per lane of that warp: n_far <= 128
+#define AR_PD 32       // look-ahead of the global prefetch [steps]
+#define AR_PS 64       // slots of the prefetch rings (a slot is reused AR_PS steps later)
+#define AR_PW 24       // cp.async groups allowed in flight: what was issued more than AR_PW steps ago has landed
+#define AR_BZ_ROWS 64  // rows per CTA the B z ring holds (7 row warps x 8 rows at L = 4)
 template <int L, int MP, int MC = -1, int CL = 0, int NT = AR_THREADS>
 __global__ void __launch_bounds__(NT, 1)
     ar_chain_v4_kernel(const double* __restrict__ A, const int* __restrict__ esi, const int* __restrict__ csi,
-                       double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl, int n_ring, int fence_mask) {
+                       double* buffer, int n_ext, int n_cs, int n_sample, int n_near, int cl, int n_ring, int fence_mask,
+                       int ring_doubles) {
   constexpr int RPW = 32 / L;  // rows per warp
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int gs = L * MP;                                     // padded length of one gather vector
@@ -325,6 +335,13 @@ __global__ void __launch_bounds__(NT, 1)
   const int n_far = n_sample - n_near;
   int* roff = pos + 3 * n_cs;                                // [n_ring + 1]: start of the delay line of far sample f
   double* ring = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(roff + n_ring + 1) + 15) & ~(uintptr_t)15);
+  // Everything a step needs from BUFFER in global memory -- the row's own B z term and the far samples beyond the delay lines
+  // -- is fetched AR_PD steps ahead by the far warp with cp.async into two rings of AR_PS slots, so that no warp ever waits
+  // for a global load: under a synthesis kernel that saturates HBM those loads take microseconds, and with a look-ahead of
+  // two to four steps the chain ran at half speed (1.08 instead of 0.54 us/step, profiles/r02_chain_under_load.txt).
+  double* bzr = ring + ring_doubles;                        // [AR_PS][AR_BZ_ROWS]: B z of step j for the rows of this CTA
+  double* fstage = bzr + AR_PS * AR_BZ_ROWS;                // [AR_PS][n_glob]: far samples of the vector of step j
+  const int n_glob = n_far - n_ring;
   int cta = 0;
   if (cl > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta));
   const int rpc = (n_cs + cl - 1) / cl;
@@ -388,12 +405,12 @@ __global__ void __launch_bounds__(NT, 1)
   // is only safe once the producer's store is known to be visible; a store followed by st.async carries no such guarantee
   // (measured: with 0.5 us steps and a synthesis kernel loading the memory system, the offset-5 samples, read one step after
   // they were produced, came back stale).  So the first n_ring far samples (the host checks that they include every offset
-  // below 64) never touch global memory: every CTA receives the whole row i + 1 in the LATE part of its gather vector of
+  // below 600) never touch global memory: every CTA receives the whole row i + 1 in the LATE part of its gather vector of
   // step i, the thread that owns far sample f copies (i + 1, c_f) from there into a private ring of d_f - 3 entries and
   // takes out (i - 2 + d_f, c_f), stored d_f - 3 steps earlier, which it sends into the vector of step i - 2.  The remaining
-  // samples (offset >= 70, i.e. read >= 66 steps after they were produced) keep the global path, ordered by a
-  // __threadfence() of every thread every (fence_mask + 1) <= 64 steps: the store of row j is followed by a fence at most 63
-  // steps later, the fence by the thread's next st.async, and the reader has waited on a barrier those bytes completed.
+  // samples (offset >= 600, i.e. read >= 566 steps after they were produced) keep the global path, ordered by a
+  // __threadfence() of every storing thread every (fence_mask + 1) = 512 steps: the store of row j is followed by a fence at
+  // most 511 steps later, the fence by the thread's next st.async, and the reader has waited on a barrier those bytes completed.
   if (tid == 0) {
     int used = 0;
     for (int f = 0; f < n_ring; f++) {
@@ -466,23 +483,18 @@ __global__ void __launch_bounds__(NT, 1)
       G[(i_top & 3) * gs + f] = buffer[(size_t)i_top * n_cs + foff[q]];
       if (i_top >= 1) G[((i_top - 1) & 3) * gs + f] = buffer[(size_t)(i_top - 1) * n_cs + foff[q]];
     }
-  // Register pipelines, two sets each, used alternately by even / odd steps (the loop is unrolled by two):
-  //   far_s[i & 1]: issued at step i + 4 for step i - 2, sent into G at step i, then re-issued for step i - 4
-  //   bz_s[i & 1] : issued at step i + 2 for step i, consumed when step i publishes, then re-issued for step i - 2
-  double far_s[2][AR_FAR_Q], bz_s[2];
-#pragma unroll
-  for (int q = 0; q < AR_FAR_Q; q++) far_s[0][q] = far_s[1][q] = 0.0;
-  bz_s[0] = bz_s[1] = 0.0;
-  if (has_row) {  // i_top is odd: set 1 serves step i_top, set 0 step i_top - 1
-    bz_s[1] = buffer[(size_t)i_top * n_cs + row0 + r];
-    bz_s[0] = buffer[(size_t)(i_top - 1) * n_cs + row0 + r];
+  // prologue of the prefetch rings: B z of steps i_top ... i_top - AR_PD + 1 and the far samples (beyond the delay lines) of the
+  // vectors of steps i_top - 2 ... i_top - 1 - AR_PD, with plain loads (initial noise and B z, written by earlier kernels);
+  // the far warp continues from there, one step per step
+  for (int e = tid; e < AR_PD * rows; e += NTT) {
+    const int j = i_top - e / rows, rl = e % rows;
+    if (j >= 0) bzr[(j & (AR_PS - 1)) * AR_BZ_ROWS + rl] = buffer[(size_t)j * n_cs + row0 + rl];
   }
-#pragma unroll
-  for (int q = 0; q < AR_FAR_Q; q++)
-    if (foff[q] >= 0) {
-      if (i_top >= 2) far_s[1][q] = buffer[(size_t)(i_top - 2) * n_cs + foff[q]];
-      if (i_top >= 3) far_s[0][q] = buffer[(size_t)(i_top - 3) * n_cs + foff[q]];
-    }
+  for (int e = tid; e < AR_PD * n_glob; e += NTT) {
+    const int j = i_top - 2 - e / n_glob, g = e % n_glob, sf = n_near + n_ring + g;
+    if (j >= 0) fstage[(j & (AR_PS - 1)) * n_glob + g] = buffer[(size_t)j * n_cs + (size_t)(esi[sf] + 1) * n_cs + csi[sf]];
+  }
+  const uint32_t bzr_s = smem_u32(bzr), fstage_s = smem_u32(fstage);
   // bytes each barrier expects for step j = i_top - d: what the loop (not the prologue) delivers
   // ONE transaction barrier per step: everything sent during step j + 1 -- row j + 1 at its offsets 1, 2, 3 (vectors of
   // steps j, j - 1, j - 2) and the far samples of the vector of step j - 1 -- completes bytes on the barrier step j waits for.
@@ -555,11 +567,13 @@ __global__ void __launch_bounds__(NT, 1)
 #endif
     // `phase` = i & 3, the gather vector of step i: a compile-time constant in the steady state (the loop below is unrolled
     // by four), so that every shared-memory address of the step is a register plus an immediate
-    auto step = [&](auto guard, auto phase, const int i, double& bz) {
+    auto step = [&](auto guard, auto phase, const int i) {
       constexpr bool GD = decltype(guard)::value;
       const int PH = phase_value(phase), PH1 = (PH + 3) & 3, PH2 = (PH + 2) & 3, PH3 = (PH + 1) & 3;  // steps i, i - 1, i - 2, i - 3
       const int ncl = CL > 0 ? CL : cl;
       const uint32_t par = ((i_top - i) >> 2) & 1;
+      // B z of this row and step: prefetched into shared memory by the far warp long ago
+      const double bz = lds_f64(bzr_s + 8u * ((i & (AR_PS - 1)) * AR_BZ_ROWS + min(r, AR_BZ_ROWS - 1)));
       // (1) the row just produced has landed in G[i]
       AR_TRACE(0, pre[0]);
       mbar_wait_cluster(bars_s + 8 * PH, par);
@@ -640,7 +654,6 @@ __global__ void __launch_bounds__(NT, 1)
       // (4) off the critical path: the periodic fence that orders this thread's row stores for the far warp's reads of BUFFER,
       //     and B z for step i - 2 (the far samples themselves are the far warp's business)
       if (fence_mask >= 0 && (i & fence_mask) == 0) __threadfence();
-      if ((!GD || i >= 2) && has_row) bz = __ldcg(buffer + (uint32_t)((i - 2) * n_cs + myrow));
       // (5) the EARLY part of step i - 1, while the row of step i is on its way
       if (!GD || i >= 1) {
         early_part(PH1, pre);
@@ -655,46 +668,63 @@ __global__ void __launch_bounds__(NT, 1)
     while (true) {
       if ((i & 3) == 3)
         for (; i >= 8; i -= 4) {
-          step(std::false_type{}, PhaseConst<3>{}, i, bz_s[1]);
-          step(std::false_type{}, PhaseConst<2>{}, i - 1, bz_s[0]);
-          step(std::false_type{}, PhaseConst<1>{}, i - 2, bz_s[1]);
-          step(std::false_type{}, PhaseConst<0>{}, i - 3, bz_s[0]);
+          step(std::false_type{}, PhaseConst<3>{}, i);
+          step(std::false_type{}, PhaseConst<2>{}, i - 1);
+          step(std::false_type{}, PhaseConst<1>{}, i - 2);
+          step(std::false_type{}, PhaseConst<0>{}, i - 3);
         }
       if (i < 1) break;
-      step(std::true_type{}, i & 3, i, bz_s[1]);
-      step(std::true_type{}, (i - 1) & 3, i - 1, bz_s[0]);
+      step(std::true_type{}, i & 3, i);
+      step(std::true_type{}, (i - 1) & 3, i - 1);
       i -= 2;
     }
   }
-  if (far_warp && n_far > 0) {
+  if (far_warp) {
     // The far warp.  Step i: wait for the barrier of step i (row i + 1 is complete in the LATE part of this CTA's vector of
     // step i), move every delay line on by one, send the far values of the vector of step i - 2 (bytes complete on the
-    // barrier of step i - 1, like everything else sent during step i).  Samples beyond the delay lines (offset >= 70) come
-    // from BUFFER, loaded four steps ahead into two register sets used by even / odd steps.
+    // barrier of step i - 1, like everything else sent during step i).  Samples beyond the delay lines (offset >= 600) come
+    // from BUFFER through the prefetch ring, like the B z terms of the CTA's rows.
     const uint32_t bars_self = mapa_u32(bars_s, cta);
     const uint32_t far_self = mapa_u32(G_s, cta) + 8u * (n_near + lane);
-    auto far_step = [&](const int i, double(&fs)[AR_FAR_Q]) {
+    int gidx[AR_FAR_Q];  // index among the samples beyond the delay lines
+#pragma unroll
+    for (int q = 0; q < AR_FAR_Q; q++) gidx[q] = lane + 32 * q - n_ring;
+    auto far_step = [&](const int i) {
       const int PH = i & 3, PH1 = (PH + 3) & 3, PH2 = (PH + 2) & 3;
       mbar_wait_cluster(bars_s + 8 * PH, ((i_top - i) >> 2) & 1);
+      // prefetch, AR_PD steps ahead: B z of step i - AR_PD for the rows of this CTA, far samples of the vector of step
+      // i - 2 - AR_PD (rows produced >= 566 steps ago, behind the row warps' periodic fence)
+      const int jb = i - AR_PD, jf = i - 2 - AR_PD;
+      if (jb >= 0) {
+#pragma unroll
+        for (int hh = 0; hh < AR_BZ_ROWS / 32; hh++) {
+          const int rl = lane + 32 * hh;
+          if (rl < rows) cp_async_f64(bzr_s + 8u * ((jb & (AR_PS - 1)) * AR_BZ_ROWS + rl), buffer + (uint32_t)(jb * n_cs + row0 + rl));
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < AR_FAR_Q; q++)
+        if (foff[q] >= 0 && ring_hi[q] == 0u && jf >= 0)
+          cp_async_f64(fstage_s + 8u * ((jf & (AR_PS - 1)) * n_glob + gidx[q]), buffer + (uint32_t)(jf * n_cs + foff[q]));
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group %0;" ::"n"(AR_PW) : "memory");  // everything issued more than AR_PW steps ago has landed
       const uint32_t be = bars_self + 8u * PH1;
 #pragma unroll
       for (int q = 0; q < AR_FAR_Q; q++)
         if (foff[q] >= 0) {
-          double v = fs[q];
+          double v;
           if (ring_hi[q] != 0u) {  // delay line: take (i - 2 + d, c) out, put (i + 1, c) in its place
             const double vnew = lds_f64(G_s + 8u * (PH * gs) + ring_src[q]);
             v = lds_f64(ring_p[q]);
             sts_f64(ring_p[q], vnew);
             ring_p[q] = ring_p[q] == ring_lo[q] ? ring_hi[q] : ring_p[q] - 8u;
+          } else {
+            v = lds_f64(fstage_s + 8u * (((i - 2) & (AR_PS - 1)) * n_glob + gidx[q]));
           }
           if (i >= 2) st_async_f64(far_self + 8u * (PH2 * gs + 32 * q), v, be);
-          if (ring_hi[q] == 0u && i >= 4) fs[q] = __ldcg(buffer + (uint32_t)((i - 4) * n_cs + foff[q]));
         }
     };
-    for (int i = i_top; i >= 1; i -= 2) {  // i_top is odd
-      far_step(i, far_s[1]);
-      far_step(i - 1, far_s[0]);
-    }
+    for (int i = i_top; i >= 0; i--) far_step(i);
   }
   // no CTA may leave while values are still on their way to it
   cluster_barrier();
@@ -705,7 +735,8 @@ static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, cons
                            int n_cs, int n_sample, int n_near, int cl, const matm_handle::ArStencil& sten,
                            cudaStream_t stream) {
   const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16 +
-                      ((size_t)sten.n_ring + 1) * sizeof(int) + 16 + (size_t)sten.ring_doubles * sizeof(double);
+                      ((size_t)sten.n_ring + 1) * sizeof(int) + 16 + (size_t)sten.ring_doubles * sizeof(double) +
+                      (size_t)AR_PS * (AR_BZ_ROWS + (size_t)(n_sample - n_near - sten.n_ring)) * sizeof(double);
   auto kernel = ar_chain_v4_kernel<L, MP, -1, 0, NT>;
   if constexpr (L == 8 && NT == 256) {
     // the production shape of every process wider than one CTA: 7 row warps x 4 rows = 28 rows per CTA.  mc = ceil(n_cs / 32)
@@ -732,7 +763,8 @@ static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, cons
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, kernel, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl, sten.n_ring, sten.fence_mask));
+  MATM_CUDA(h, cudaLaunchKernelEx(&cfg, kernel, A, esi, csi, buffer, n_ext, n_cs, n_sample, n_near, cl, sten.n_ring, sten.fence_mask,
+                                  sten.ring_doubles));
   h->launches++;
   return MATM_OK;
 }
@@ -741,8 +773,9 @@ static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, cons
 // in stencil order (offsets grow), as long as their column has an offset-1 sample and the lines fit AR_RING_DOUBLES.  What is
 // left takes the global path, which needs its smallest offset to be >= AR_GLOBAL_MIN_OFFSET; otherwise the general kernel
 // (cluster barrier per step) runs the process.  The stencil is read back from the device once and cached in the handle.
-#define AR_RING_DOUBLES 8192
-#define AR_GLOBAL_MIN_OFFSET 70  // fence every 64 steps + 4 steps of look-ahead + 2
+#define AR_RING_DOUBLES 12288
+#define AR_FENCE_STEPS 512
+#define AR_GLOBAL_MIN_OFFSET 600  // fence every 512 steps + AR_PD + 2 steps of look-ahead + margin
 static int ar_stencil_info(matm_handle* h, const int32_t* esi_dev, const int32_t* csi_dev, int n_cs, int n_sample, int n_near,
                            matm_handle::ArStencil* out) {
   const auto key = std::make_pair((const void*)esi_dev, ((int64_t)n_sample << 32) | (uint32_t)n_near);
@@ -773,7 +806,7 @@ static int ar_stencil_info(matm_handle* h, const int32_t* esi_dev, const int32_t
     if (f < n_sample) {
       int dmin = INT32_MAX;
       for (int g = f; g < n_sample; g++) dmin = min(dmin, esi[g] + 1);
-      st.fence_mask = 63;
+      st.fence_mask = AR_FENCE_STEPS - 1;
       if (dmin < AR_GLOBAL_MIN_OFFSET) st.ok = 0;
     }
   }

@@ -20,6 +20,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", default="c4")
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--load", action="store_true", help="time the chains underneath a copy loop that saturates HBM")
     args = ap.parse_args()
     dur = 3600.0 if args.config == "c4" else 6 * 3600.0
     cfg = configs.c4_atlast(n_det=2048, duration=dur, sample_rate=50.0)
@@ -32,6 +33,10 @@ def main():
     atm.drain() if hasattr(atm, "drain") else None
     torch.cuda.synchronize()
     ref = {}
+    side = torch.cuda.Stream()
+    if args.load:
+        src = torch.empty(1 << 28, dtype=torch.float32, device="cuda").normal_()
+        dst = torch.empty_like(src)
     for k, p in atm.processes.items():
         dv = p._dev
         n_ext, n_cs = p.n_extrusion, p.n_cross_section
@@ -44,6 +49,11 @@ def main():
             best = 1e30
             for _ in range(args.reps):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                if args.load:
+                    side.wait_stream(torch.cuda.current_stream())
+                    with torch.cuda.stream(side):
+                        for _ in range(int(3 * 2 * n_ext * 1e-3 / 0.35) + 20):  # ~0.35 ms per 1 GiB copy: 3 us per chain step
+                            dst.copy_(src)
                 e0.record()
                 ctx.check(ctx.lib.matm_ar_generate(ctx.h, n_ext, n_cs, p.n_sample, p.n_near, dv["A"].data_ptr(), dv["B"].data_ptr(),
                                                    dv["esi"].data_ptr(), dv["csi"].data_ptr(), buf.data_ptr(), zz.data_ptr(), st))
