@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--chunk-mib", type=int, default=None, help="scratch per detector chunk of the two-kernel synthesis [MiB]")
     ap.add_argument("--chunk-serial", action="store_true", help="run the detector chunks of one synthesis on one stream")
     ap.add_argument("--kernel-times", action="store_true", help="bracket every launch of the two synthesis kernels with events")
+    ap.add_argument("--nccl-max-ctas", type=int, default=2, help="CTAs NCCL may use per collective (the layer exchange)")
     ap.add_argument("--no-overlap", action="store_true",
                     help="generate and synthesise strictly one after the other (default: the AR chains of realisation i+1 run "
                          "underneath the synthesis kernels of realisation i)")
@@ -528,7 +529,7 @@ def run_b200(args):
         # NCCL kernels waiting for a peer must not hold the SMs the synthesis runs on
         opts = dist.ProcessGroupNCCL.Options()
         try:
-            opts.config.min_ctas, opts.config.max_ctas = 1, 2
+            opts.config.min_ctas, opts.config.max_ctas = 1, args.nccl_max_ctas
         except Exception:
             pass
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"), pg_options=opts)
