@@ -426,7 +426,7 @@ class Atmosphere:
 
     def generate_async(self):
         """Start the AR recurrences of all processes for one more realisation, on their own high-priority streams (one
-        stream per process and pipeline slot: the recurrences are independent sequential chains of 1-3 CTAs each and
+        stream per process and pipeline slot: the recurrences are independent sequential chains of 1-6 CTAs each and
         run side by side).  Nothing the sampler reads is touched, so a synthesis of an EARLIER realisation enqueued after
         this call overlaps with the chains: up to ``pipeline_depth`` realisations are generated underneath the synthesis
         kernels.  ``finish_generate`` completes the oldest one."""
@@ -439,7 +439,7 @@ class Atmosphere:
         cur = tc.cuda.current_stream(ctx.device)
         fork = cur.record_event()
         if not hasattr(self, "_streams"):
-            # high priority: a chain CTA needs a whole SM (512 threads x 128 registers), so when it runs underneath a
+            # high priority: a chain CTA needs a whole SM (256 threads x ~190 registers, ~150 KB of shared memory), so when it runs underneath a
             # synthesis kernel it must be first in line for the SMs that drain
             self._streams = {(s, k): tc.cuda.Stream(device=ctx.device, priority=-1)
                              for s in range(self.pipeline_depth) for k in self.processes}
