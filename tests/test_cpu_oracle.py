@@ -178,3 +178,27 @@ def test_empty_and_degenerate_inputs_raise():
     np.random.seed(1)
     with pytest.raises(Exception):
         O.simulate(case["instrument"], case["plan"], case["site"], case["weather"], case["spectrum"], np.random)
+
+
+@pytest.mark.parametrize("name", ["m2_daisy", "1deg_ces"])
+def test_as_run_float32_variant_stays_within_the_fp32_bound_of_the_float64_oracle(name):
+    """The reference hands its interpolators to jax with x64 disabled; the oracle's ``f32=True`` variant casts where the
+    reference does.  On the same geometry and the same generated layers it must sit within the bound this repo states for
+    its own float32 device path (tests/common.py), i.e. the reference-as-run and the CUDA path are equally far from the
+    float64 reference (scripts/fp32_asrun_table.py)."""
+    import importlib.util
+    import os
+
+    from common import TOL32_FLUCT, TOL32_TAIL, load_case
+
+    spec = importlib.util.spec_from_file_location(
+        "fp32_asrun_table", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts", "fp32_asrun_table.py"))
+    table = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(table)
+    case = load_case(name)
+    ref, as_run, stored, stages = table.as_run_pair(case, case["seed"])
+    assert as_run.dtype == np.float32 and as_run.shape == ref.shape
+    assert table.rel(stored, ref) < 1e-7                  # storage alone: half an ulp of float32
+    assert 1e-8 < table.rel(as_run, ref) < TOL32_TAIL     # the casts do something, and stay inside the stated bound
+    assert table.fluct(as_run, ref) < TOL32_FLUCT
+    assert stages["zenith_scaled_pwv"] < 1e-6 and stages["az"] < 1e-6 and stages["el"] < 1e-6
