@@ -70,7 +70,9 @@ int matm_fill_normal(matm_handle* h, double* out_dev, size_t n, uint64_t seed, u
  * A_dev (n_cs, n_sample), B_dev (n_cs, n_cs) float64 row-major; esi_dev/csi_dev (n_sample,) int32 are
  * extrusion_sample_index / cross_section_sample_index (process.py:44-67), esi non-decreasing as the reference builds
  * it.  n_near = number of leading stencil samples with esi + 1 <= 3 (they are served from an on-chip ring of the last
- * three rows); pass -1 to force the generic kernel. */
+ * three rows); pass -1 to force the generic kernel.  The first call for a stencil (device pointer of esi + shape) copies
+ * esi / csi back to the host once (a blocking cudaMemcpy) to size the on-chip delay lines of the far samples and caches the
+ * result in the handle: the stencil arrays must not change behind the same pointer while the handle lives. */
 int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sample, int n_near, const double* A_dev, const double* B_dev,
                      const int32_t* esi_dev, const int32_t* csi_dev, double* buffer_dev, const double* z_dev,
                      void* stream);

@@ -730,13 +730,18 @@ __global__ void __launch_bounds__(NT, 1)
   cluster_barrier();
 }
 
+// dynamic shared memory of the register-resident kernel: gather vectors, barriers, stencil maps, delay lines, prefetch rings
+static size_t chain_v4_smem(int L, int MP, int n_cs, int n_sample, int n_near, const matm_handle::ArStencil& sten) {
+  return 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16 +
+         ((size_t)sten.n_ring + 1) * sizeof(int) + 16 + (size_t)sten.ring_doubles * sizeof(double) +
+         (size_t)AR_PS * (AR_BZ_ROWS + (size_t)(n_sample - n_near - sten.n_ring)) * sizeof(double);
+}
+
 template <int L, int MP, int NT>
 static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, const int* csi, double* buffer, int n_ext,
                            int n_cs, int n_sample, int n_near, int cl, const matm_handle::ArStencil& sten,
                            cudaStream_t stream) {
-  const size_t smem = 4 * (size_t)L * MP * sizeof(double) + 3 * (size_t)n_cs * sizeof(int) + 16 + 8 * sizeof(uint64_t) + 16 +
-                      ((size_t)sten.n_ring + 1) * sizeof(int) + 16 + (size_t)sten.ring_doubles * sizeof(double) +
-                      (size_t)AR_PS * (AR_BZ_ROWS + (size_t)(n_sample - n_near - sten.n_ring)) * sizeof(double);
+  const size_t smem = chain_v4_smem(L, MP, n_cs, n_sample, n_near, sten);
   auto kernel = ar_chain_v4_kernel<L, MP, -1, 0, NT>;
   if constexpr (L == 8 && NT == 256) {
     // the production shape of every process wider than one CTA: 7 row warps x 4 rows = 28 rows per CTA.  mc = ceil(n_cs / 32)
@@ -776,9 +781,10 @@ static int launch_chain_v4(matm_handle* h, const double* A, const int* esi, cons
 #define AR_RING_DOUBLES 12288
 #define AR_FENCE_STEPS 512
 #define AR_GLOBAL_MIN_OFFSET 600  // fence every 512 steps + AR_PD + 2 steps of look-ahead + margin
-static int ar_stencil_info(matm_handle* h, const int32_t* esi_dev, const int32_t* csi_dev, int n_cs, int n_sample, int n_near,
-                           matm_handle::ArStencil* out) {
-  const auto key = std::make_pair((const void*)esi_dev, ((int64_t)n_sample << 32) | (uint32_t)n_near);
+static int ar_stencil_info(matm_handle* h, const int32_t* esi_dev, const int32_t* csi_dev, int n_ext, int n_cs, int n_sample,
+                           int n_near, matm_handle::ArStencil* out) {
+  const int64_t shape = (((int64_t)n_sample * 1000003 + n_near) * 1000003 + n_ext) * 1000003 + n_cs;
+  const auto key = std::make_pair((const void*)esi_dev, shape);
   auto it = h->ar_stencil.find(key);
   if (it != h->ar_stencil.end()) {
     *out = it->second;
@@ -874,8 +880,10 @@ extern "C" int matm_ar_generate(matm_handle* h, int n_ext, int n_cs, int n_sampl
     int L, mp, cl3, nt;
     matm_handle::ArStencil sten = {0, 0, -1, 0};
     if (n_near >= 0 && n_near <= n_sample && n_ext >= 4 && plan_v4(n_cs, n_sample, n_sample - n_near, &L, &mp, &cl3, &nt)) {
-      int rc = ar_stencil_info(h, esi_dev, csi_dev, n_cs, n_sample, n_near, &sten);
+      int rc = ar_stencil_info(h, esi_dev, csi_dev, n_ext, n_cs, n_sample, n_near, &sten);
       if (rc) return rc;
+      // 227 KB of shared memory per CTA on sm_100: a stencil whose rings do not fit runs on the general kernel
+      if (chain_v4_smem(L, mp, n_cs, n_sample, n_near, sten) > (size_t)225 * 1024) sten.ok = 0;
     }
     if (sten.ok) {
 #define V4_CASE(LV, MV, NV) \
