@@ -232,7 +232,8 @@ def run_reference(args):
         "impl": "reference", "metric": "atmospheric TOD detector-samples/sec", "value": cpu["value"], "unit": "detector-samples/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": wall * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args, cfg, args.n_det), "sample": cpu["sample"]},
+        "config": {"workload": workload_name(args, cfg, args.n_det if args.config == "c4" else cfg["instrument"].dets.n // max(1, args.gpus)),
+                   "sample": cpu["sample"]},
         "cpu_baseline": cpu,
         "e2e": {"value": cpu["value"], "unit": "detector-samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
